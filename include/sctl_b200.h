@@ -1,0 +1,138 @@
+/* sctl_b200.h — C ABI of the B200-native direct particle-kernel summation library.
+ *
+ * This is the drop-in boundary for ONE hot path of SCTL (reference tree: /root/reference):
+ *
+ *   GenericKernel<uKernel>::Eval (static, type-erased, runtime digits)  include/sctl/generic-kernel.txx:46-74
+ *   GenericKernel<uKernel>::Eval<Real,enable_openmp,digits>             include/sctl/generic-kernel.txx:76-189
+ *   GenericKernel<uKernel>::KernelMatrix<Real,enable_openmp,digits>     include/sctl/generic-kernel.txx:191-307
+ *   CoordDim/NormalDim/SrcDim/TrgDim, Name(), FLOPS(), uKerScaleFactor  include/sctl/generic-kernel.txx:22-36,
+ *                                                                       include/sctl/kernel_functions.hpp:16-25 ...
+ *   the per-rank body of ParticleFMM::EvalDirect                        include/sctl/fmm-wrapper.txx:490-562
+ *
+ * The reference is a header-only C++ template library; the binding a maintainer adds is the header
+ * include/sctl_b200/generic-kernel-b200.hpp (explicit specialisations of the member templates above that
+ * forward here) — see INTEGRATION.md.
+ *
+ * Conventions
+ *  - Plain C types only. All arrays are contiguous AoS exactly as the reference's Vector<Real> holds them:
+ *      r_trg[Nt*3] = {x0,y0,z0,x1,...}   r_src[Ns*3]   n_src[Ns*NormalDim]   v_src[Ns*SrcDim]   v_trg[Nt*TrgDim]
+ *    n_src may be NULL iff NormalDim == 0 (generic-kernel.txx:97).
+ *  - dX = x_trg - x_src (generic-kernel.txx:83); pairs with |dX|^2 == 0 contribute exactly 0
+ *    (kernel_functions.hpp:28); the scale factor is applied once after the sum (generic-kernel.txx:184).
+ *  - Every function returns 0 on success or a SCTL_B200_ERR_* code; sctl_b200_last_error() returns a
+ *    thread-local message. There is NO CPU fallback: without a usable CUDA device every compute call fails
+ *    with SCTL_B200_ERR_CUDA. The reference aborts on bad sizes (generic-kernel.txx:94-97); the C++ shim maps
+ *    a non-zero return to SCTL_ERROR to preserve that.
+ *  - Thread-safe and re-entrant: the reference's KernelMatrix is called from inside OpenMP parallel regions
+ *    (boundary_integral.txx:949-986). Each host thread owns its stream and device workspace.
+ *  - Results are NOT bit-identical to the CPU path (different summation order, different rsqrt refinement);
+ *    the contract is rel-L2 <= 1e-12 (f64) / 1e-5 (f32) against the reference's CPU Eval.
+ */
+#ifndef SCTL_B200_H_
+#define SCTL_B200_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define SCTL_B200_API __attribute__((visibility("default")))
+#else
+#define SCTL_B200_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* kernel ids: the eight GenericKernel typedefs of kernel_functions.hpp:207-214 */
+enum {
+  SCTL_B200_LAPLACE3D_FXU = 0,  /* kernel_functions.hpp:15-31   K 1x1, no normal, 1/(4 pi)  */
+  SCTL_B200_LAPLACE3D_DXU = 1,  /* kernel_functions.hpp:33-51   K 1x1, normal,    1/(4 pi)  */
+  SCTL_B200_LAPLACE3D_FXDU = 2, /* kernel_functions.hpp:53-72   K 1x3, no normal, -1/(4 pi) */
+  SCTL_B200_STOKES3D_FXU = 3,   /* kernel_functions.hpp:74-95   K 3x3, no normal, 1/(8 pi)  */
+  SCTL_B200_STOKES3D_DXU = 4,   /* kernel_functions.hpp:97-120  K 3x3, normal,    3/(4 pi)  */
+  SCTL_B200_STOKES3D_FXT = 5,   /* kernel_functions.hpp:122-146 K 3x9, no normal, -3/(4 pi) */
+  SCTL_B200_STOKES3D_FSXU = 6,  /* kernel_functions.hpp:148-172 K 4x3, no normal, 1/(8 pi)  */
+  SCTL_B200_STOKES3D_FXUP = 7,  /* kernel_functions.hpp:174-198 K 3x4, no normal, 1/(8 pi)  */
+  SCTL_B200_NUM_KERNELS = 8
+};
+
+/* dtype: Real of the reference's template parameter */
+enum { SCTL_B200_F32 = 0, SCTL_B200_F64 = 1 };
+
+/* flags */
+enum {
+  SCTL_B200_DEVICE_PTRS = 1u << 0, /* all pointers are device pointers on the current CUDA device */
+  SCTL_B200_OVERWRITE = 1u << 1,   /* v_trg = scale*sum instead of v_trg += scale*sum (EvalDirect zeroes U first, fmm-wrapper.txx:501-502) */
+  SCTL_B200_ALL_GPUS = 1u << 2     /* host pointers only: shard targets over every visible GPU of this process (fmm-wrapper.txx:504-510 analogue) */
+};
+
+/* error codes */
+enum {
+  SCTL_B200_OK = 0,
+  SCTL_B200_ERR_KERNEL = 1, /* unknown kernel id */
+  SCTL_B200_ERR_DTYPE = 2,  /* unknown dtype */
+  SCTL_B200_ERR_ARG = 3,    /* null pointer / negative size / bad flag combination */
+  SCTL_B200_ERR_CUDA = 4,   /* CUDA runtime error or no usable device (no CPU fallback) */
+  SCTL_B200_ERR_NOMEM = 5   /* device allocation failed */
+};
+
+/* Metadata — replaces CoordDim()/NormalDim()/SrcDim()/TrgDim() (generic-kernel.txx:22-36),
+ * uKerScaleFactor<double>() and FLOPS() (kernel_functions.hpp). Any out pointer may be NULL. No GPU needed. */
+SCTL_B200_API int sctl_b200_kernel_dims(int kernel_id, int* coord_dim, int* normal_dim, int* src_dim, int* trg_dim, double* scale, int* flops);
+/* Name() of the micro-kernel, e.g. "Stokes3D-FxU" (kernel_functions.hpp:16-19); NULL for a bad id. */
+SCTL_B200_API const char* sctl_b200_kernel_name(int kernel_id);
+
+/* Potential evaluation — replaces GenericKernel::Eval (generic-kernel.txx:46-74 -> 76-189):
+ *   v_trg[t*K1+k1] (+)= scale * sum_s sum_k0 K[k0][k1](x_t - x_s, n_s) * v_src[s*K0+k0]
+ * digits: -1 or >= 16 = machine precision; 0..15 = requested significant digits (the GPU path may deliver
+ * more, never fewer — the reference only ever relaxes the rsqrt refinement, intrin-wrapper.hpp:3026).
+ * Host pointers (default): synchronous; inputs are copied to the device, result copied back.
+ * SCTL_B200_DEVICE_PTRS: runs on the calling thread's library stream and synchronises before returning. */
+SCTL_B200_API int sctl_b200_eval(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                   const void* v_src, void* v_trg, int digits, unsigned flags);
+
+/* Same with device pointers, enqueued on a caller-supplied cudaStream_t (passed as void*; NULL = default
+ * stream) WITHOUT synchronising: for callers that keep Vector storage device-resident. */
+SCTL_B200_API int sctl_b200_eval_async(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* d_r_trg, const void* d_r_src,
+                         const void* d_n_src, const void* d_v_src, void* d_v_trg, int digits, unsigned flags, void* cuda_stream);
+
+/* Dense operator — replaces GenericKernel::KernelMatrix (generic-kernel.txx:191-307):
+ *   M[(s*K0+k0) * (Nt*K1) + (t*K1+k1)] = scale * K[k0][k1](x_t - x_s, n_s)       (row-major, every entry overwritten) */
+SCTL_B200_API int sctl_b200_kernel_matrix(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src,
+                            const void* n_src, void* M, int digits, unsigned flags);
+SCTL_B200_API int sctl_b200_kernel_matrix_async(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* d_r_trg, const void* d_r_src,
+                                  const void* d_n_src, void* d_M, int digits, unsigned flags, void* cuda_stream);
+
+/* Device-resident Vector storage (north_star: "device-resident Vector buffers"): raw device memory on the
+ * current device, usable with SCTL_B200_DEVICE_PTRS / *_async. */
+SCTL_B200_API int sctl_b200_buf_create(void** d_ptr, int dtype, int64_t n);
+SCTL_B200_API int sctl_b200_buf_upload(void* d_ptr, const void* host, int dtype, int64_t n);
+SCTL_B200_API int sctl_b200_buf_download(const void* d_ptr, void* host, int dtype, int64_t n);
+SCTL_B200_API int sctl_b200_buf_destroy(void* d_ptr);
+
+/* Device management. One process per GPU is the normal multi-GPU mode (each MPI / torchrun rank calls
+ * sctl_b200_set_device(local_rank) once, as the reference's ranks each own a target block,
+ * fmm-wrapper.txx:504-510). */
+SCTL_B200_API int sctl_b200_device_count(int* n);
+SCTL_B200_API int sctl_b200_set_device(int dev);
+SCTL_B200_API int sctl_b200_get_device(int* dev);
+SCTL_B200_API int sctl_b200_sm_count(int* n);
+
+/* Measurement helpers (bench.py): number of kernel launches this library has issued from this process, and a
+ * register-resident DFMA / FFMA chain that measures the CUDA-core FP64 / FP32 peak used as roofline
+ * denominator (MEASURED_PEAKS.json has no such figure). Runs for about `seconds`; reports TFLOP/s counting
+ * one FMA as 2 flops. */
+SCTL_B200_API int64_t sctl_b200_launch_count(void);
+SCTL_B200_API int sctl_b200_measure_peak(int dtype, double seconds, double* tflops);
+
+/* Timing of the most recent eval / kernel_matrix issued by this thread through the HOST-pointer entry points:
+ * milliseconds spent in (h2d, pack, main kernel, reduce, d2h), measured with CUDA events. */
+SCTL_B200_API int sctl_b200_last_timing(double ms[5]);
+
+SCTL_B200_API const char* sctl_b200_last_error(void);
+SCTL_B200_API const char* sctl_b200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCTL_B200_H_ */

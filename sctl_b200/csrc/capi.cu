@@ -1,0 +1,554 @@
+// C ABI of libsctl_b200.so (declared in include/sctl_b200.h): argument checking, per-thread streams,
+// stream-ordered device workspaces, the pack -> eval -> reduce launch plan, host<->device staging and the
+// in-process multi-GPU target sharding. No CPU fallback anywhere: a missing device is an error.
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/sctl_b200.h"
+#include "launch.h"
+
+namespace sctl_b200 {
+
+// ------------------------------------------------------------------------------------------------
+// bookkeeping
+// ------------------------------------------------------------------------------------------------
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+static thread_local std::string t_last_error;
+static thread_local double t_timing[5] = {0, 0, 0, 0, 0};
+
+static int set_error(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  t_last_error = buf;
+  return code;
+}
+static int cuda_error(cudaError_t e, const char* what) {
+  return set_error(SCTL_B200_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+}
+#define CU_TRY(call)                                       \
+  do {                                                     \
+    cudaError_t e__ = (call);                              \
+    if (e__ != cudaSuccess) return cuda_error(e__, #call); \
+  } while (0)
+
+struct KernelInfo {
+  const char* name;
+  int normal_dim, src_dim, trg_dim, flops;
+  double scale_num, scale_den_pi;
+};
+// kernel_functions.hpp:15-198 (Name, FLOPS, uKerScaleFactor) and the dims deduced by generic-kernel.hpp:33-52
+static const KernelInfo KINFO[NUM_KERNELS] = {
+    {"Laplace3D-FxU", 0, 1, 1, 6, 1.0, 4.0},    {"Laplace3D-DxU", 3, 1, 1, 14, 1.0, 4.0}, {"Laplace3D-FxdU", 0, 1, 3, 11, -1.0, 4.0},
+    {"Stokes3D-FxU", 0, 3, 3, 23, 1.0, 8.0},    {"Stokes3D-DxU", 3, 3, 3, 26, 3.0, 4.0},  {"Stokes3D-FxT", 0, 3, 9, 39, -3.0, 4.0},
+    {"Stokes3D-FSxU", 0, 4, 3, 26, 1.0, 8.0},   {"Stokes3D-FxUP", 0, 3, 4, 26, 1.0, 8.0},
+};
+static double kernel_scale(int kid) {
+  return (double)((long double)KINFO[kid].scale_num / ((long double)KINFO[kid].scale_den_pi * 3.14159265358979323846264338327950288L));
+}
+
+// digits -> rsqrt refinement level (common.cuh). The reference relaxes the Newton count with digits
+// (intrin-wrapper.hpp:3026); we never deliver fewer digits than asked for.
+static int newton_level(int dtype, int digits) {
+  if (dtype == SCTL_B200_F64) {
+    if (digits < 0 || digits > 12) return 2;
+    return digits > 6 ? 1 : 0;
+  }
+  return (digits < 0 || digits > 6) ? 1 : 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-thread, per-device context: one non-blocking stream + timing events
+// ------------------------------------------------------------------------------------------------
+struct DevCtx {
+  int dev = -1;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  int sms = 0;
+};
+static thread_local std::vector<DevCtx> t_ctx;
+static std::mutex g_pool_mutex;
+static std::vector<int> g_pool_configured;
+
+static int get_ctx(DevCtx** out) {
+  int dev = 0;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev < 1) {
+    cudaGetLastError();
+    return set_error(SCTL_B200_ERR_CUDA, "no usable CUDA device (%s); libsctl_b200 has no CPU fallback",
+                     e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  }
+  CU_TRY(cudaGetDevice(&dev));
+  for (auto& c : t_ctx)
+    if (c.dev == dev) {
+      *out = &c;
+      return 0;
+    }
+  DevCtx c;
+  c.dev = dev;
+  CU_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  for (auto& ev : c.ev) CU_TRY(cudaEventCreate(&ev));
+  CU_TRY(cudaDeviceGetAttribute(&c.sms, cudaDevAttrMultiProcessorCount, dev));
+  {
+    // keep stream-ordered allocations cached in the default pool instead of returning them at every sync
+    std::lock_guard<std::mutex> lk(g_pool_mutex);
+    bool done = false;
+    for (int d : g_pool_configured) done |= (d == dev);
+    if (!done) {
+      cudaMemPool_t pool;
+      if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+      }
+      g_pool_configured.push_back(dev);
+    }
+  }
+  t_ctx.push_back(c);
+  *out = &t_ctx.back();
+  return 0;
+}
+
+static size_t elem_size(int dtype) { return dtype == SCTL_B200_F64 ? 8 : 4; }
+
+static int check_common(int kernel_id, int dtype, int64_t Nt, int64_t Ns) {
+  if (kernel_id < 0 || kernel_id >= NUM_KERNELS) return set_error(SCTL_B200_ERR_KERNEL, "unknown kernel id %d", kernel_id);
+  if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return set_error(SCTL_B200_ERR_DTYPE, "unknown dtype %d", dtype);
+  if (Nt < 0 || Ns < 0) return set_error(SCTL_B200_ERR_ARG, "negative size Nt=%lld Ns=%lld", (long long)Nt, (long long)Ns);
+  return 0;
+}
+
+struct DevAlloc {  // stream-ordered allocation, freed on the same stream
+  void* p = nullptr;
+  cudaStream_t st = nullptr;
+  ~DevAlloc() {
+    if (p) cudaFreeAsync(p, st);
+  }
+  int alloc(size_t bytes, cudaStream_t s) {
+    st = s;
+    cudaError_t e = cudaMallocAsync(&p, bytes ? bytes : 16, s);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      cudaGetLastError();
+      return set_error(SCTL_B200_ERR_NOMEM, "cudaMallocAsync(%zu bytes): %s", bytes, cudaGetErrorString(e));
+    }
+    return 0;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// launch plan for Eval on device-resident AoS arrays
+// ------------------------------------------------------------------------------------------------
+struct EvalPlan {
+  int rvar, newton, n_chunks, tiles_per_chunk;
+  long long n_tiles, n_ttiles, Ns_pad, nt_stride;
+};
+
+static int env_int(const char* name, int dflt) {
+  const char* s = getenv(name);
+  return (s && *s) ? atoi(s) : dflt;
+}
+
+static EvalPlan make_plan(const EvalEntry& E, int dtype, int64_t Nt, int64_t Ns, int digits, int sms) {
+  EvalPlan P{};
+  P.newton = newton_level(dtype, digits);
+  // small target sets use the R=1 variant so that fewer lanes idle in the ragged last tile
+  P.rvar = (Nt >= (int64_t)env_int("SCTL_B200_RBIG_MIN_NT", 2048)) ? 1 : 0;
+  const int R = E.R[P.rvar];
+  P.n_tiles = (Ns + EVAL_TILE - 1) / EVAL_TILE;
+  P.Ns_pad = P.n_tiles * EVAL_TILE;
+  P.n_ttiles = (Nt + (long long)EVAL_THREADS * R - 1) / ((long long)EVAL_THREADS * R);
+  P.nt_stride = (Nt + 31) / 32 * 32;
+  // split the source range until there are ~64 CTAs per resident slot (tail <= ~1.5 %), keeping at least
+  // 8 tiles per chunk and at most 1 GiB of partial sums
+  const int occ = E.occupancy[P.rvar][P.newton]();
+  const long long slots = (long long)occ * sms;
+  const long long want = (long long)env_int("SCTL_B200_CTAS_PER_SLOT", 64) * slots;
+  long long chunks = (want + P.n_ttiles - 1) / P.n_ttiles;
+  const long long max_by_tiles = P.n_tiles / 8 > 0 ? P.n_tiles / 8 : 1;
+  const long long max_by_mem = (long long)((1ull << 30) / ((size_t)E.k1 * 8 * (size_t)P.nt_stride));
+  if (chunks > max_by_tiles) chunks = max_by_tiles;
+  if (chunks > max_by_mem) chunks = max_by_mem;
+  if (chunks > 65535) chunks = 65535;
+  if (chunks < 1) chunks = 1;
+  const int forced = env_int("SCTL_B200_FORCE_CHUNKS", 0);
+  if (forced > 0) chunks = forced < P.n_tiles ? forced : P.n_tiles;
+  P.tiles_per_chunk = (int)((P.n_tiles + chunks - 1) / chunks);
+  P.n_chunks = (int)((P.n_tiles + P.tiles_per_chunk - 1) / P.tiles_per_chunk);
+  return P;
+}
+
+// All pointers are device pointers on the current device. Enqueues on `st`, does not synchronise.
+// ev (optional): 4 events recorded around pack | eval | reduce.
+static int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                       const void* v_src, void* v_trg, int digits, bool accumulate, cudaStream_t st, int sms, cudaEvent_t* ev) {
+  const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
+  const size_t esz = elem_size(dtype);
+  if (Nt == 0) return 0;
+  if (Ns == 0) {
+    if (!accumulate) CU_TRY(cudaMemsetAsync(v_trg, 0, (size_t)Nt * E.k1 * esz, st));
+    if (ev)
+      for (int i = 0; i < 4; i++) CU_TRY(cudaEventRecord(ev[i], st));
+    return 0;
+  }
+  if (Ns > (int64_t)EVAL_TILE * 0x7fffffffLL) return set_error(SCTL_B200_ERR_ARG, "Ns too large");
+  const EvalPlan P = make_plan(E, dtype, Nt, Ns, digits, sms);
+
+  DevAlloc rec, partial;
+  int rc = rec.alloc((size_t)P.Ns_pad * E.rec_len * esz, st);
+  if (rc) return rc;
+  if (P.n_chunks > 1) {
+    rc = partial.alloc((size_t)P.n_chunks * E.k1 * (size_t)P.nt_stride * sizeof(double), st);
+    if (rc) return rc;
+  }
+  if (ev) CU_TRY(cudaEventRecord(ev[0], st));
+  CU_TRY(E.pack(r_src, n_src, v_src, rec.p, Ns, P.Ns_pad, st));
+  if (ev) CU_TRY(cudaEventRecord(ev[1], st));
+
+  EvalParams p{};
+  p.r_trg = r_trg;
+  p.rec = rec.p;
+  p.v_trg = v_trg;
+  p.partial = (double*)partial.p;
+  p.Nt = Nt;
+  p.nt_stride = P.nt_stride;
+  p.n_tiles = (int)P.n_tiles;
+  p.tiles_per_chunk = P.tiles_per_chunk;
+  p.n_chunks = P.n_chunks;
+  p.accumulate = accumulate ? 1 : 0;
+  p.scale = kernel_scale(kernel_id);
+  CU_TRY(E.eval[P.rvar][P.newton](p, P.n_ttiles, st));
+  if (ev) CU_TRY(cudaEventRecord(ev[2], st));
+  if (P.n_chunks > 1) CU_TRY(E.reduce((const double*)partial.p, v_trg, Nt, P.nt_stride, P.n_chunks, p.scale, p.accumulate, st));
+  if (ev) CU_TRY(cudaEventRecord(ev[3], st));
+  return 0;
+}
+
+static int kmat_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src, void* M,
+                       int digits, cudaStream_t st) {
+  const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
+  if (Nt == 0 || Ns == 0) return 0;
+  const size_t esz = elem_size(dtype);
+  const int newton = newton_level(dtype, digits);
+  // grid.y is limited to 65535 blocks of KMAT_SB sources: walk the source range in slabs
+  const int64_t slab = (int64_t)65535 * KMAT_SB;
+  for (int64_t s0 = 0; s0 < Ns; s0 += slab) {
+    const int64_t ns = Ns - s0 < slab ? Ns - s0 : slab;
+    const char* rs = (const char*)r_src + (size_t)s0 * 3 * esz;
+    const char* nn = n_src ? (const char*)n_src + (size_t)s0 * E.nd * esz : nullptr;
+    char* Mp = (char*)M + (size_t)s0 * E.k0 * (size_t)Nt * E.k1 * esz;
+    CU_TRY(E.kmat[newton](r_trg, rs, nn, Mp, Nt, ns, kernel_scale(kernel_id), st));
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-pointer paths (what the C++ header shim calls): stage in, run, stage out, synchronise
+// ------------------------------------------------------------------------------------------------
+static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, a, b) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return ms;
+}
+
+static int eval_host_one_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                                const void* v_src, void* v_trg, int digits, bool accumulate) {
+  DevCtx* c = nullptr;
+  int rc = get_ctx(&c);
+  if (rc) return rc;
+  const KernelInfo& ki = KINFO[kernel_id];
+  const size_t esz = elem_size(dtype);
+  cudaStream_t st = c->stream;
+  if (Nt == 0) return 0;
+  DevAlloc d_rt, d_rs, d_ns, d_vs, d_vt;
+  const size_t b_rt = (size_t)Nt * 3 * esz, b_rs = (size_t)Ns * 3 * esz, b_ns = (size_t)Ns * ki.normal_dim * esz,
+               b_vs = (size_t)Ns * ki.src_dim * esz, b_vt = (size_t)Nt * ki.trg_dim * esz;
+  if ((rc = d_rt.alloc(b_rt, st)) || (rc = d_rs.alloc(b_rs, st)) || (rc = d_ns.alloc(b_ns, st)) || (rc = d_vs.alloc(b_vs, st)) ||
+      (rc = d_vt.alloc(b_vt, st)))
+    return rc;
+  cudaEvent_t* ev = c->ev;
+  CU_TRY(cudaEventRecord(ev[4], st));
+  CU_TRY(cudaMemcpyAsync(d_rt.p, r_trg, b_rt, cudaMemcpyHostToDevice, st));
+  if (b_rs) CU_TRY(cudaMemcpyAsync(d_rs.p, r_src, b_rs, cudaMemcpyHostToDevice, st));
+  if (b_ns) CU_TRY(cudaMemcpyAsync(d_ns.p, n_src, b_ns, cudaMemcpyHostToDevice, st));
+  if (b_vs) CU_TRY(cudaMemcpyAsync(d_vs.p, v_src, b_vs, cudaMemcpyHostToDevice, st));
+  if (accumulate) CU_TRY(cudaMemcpyAsync(d_vt.p, v_trg, b_vt, cudaMemcpyHostToDevice, st));
+  rc = eval_device(kernel_id, dtype, Nt, Ns, d_rt.p, d_rs.p, d_ns.p, d_vs.p, d_vt.p, digits, accumulate, st, c->sms, ev);
+  if (rc) return rc;
+  CU_TRY(cudaMemcpyAsync(v_trg, d_vt.p, b_vt, cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaEventRecord(ev[5], st));
+  CU_TRY(cudaStreamSynchronize(st));
+  t_timing[0] = ev_ms(ev[4], ev[0]);
+  t_timing[1] = ev_ms(ev[0], ev[1]);
+  t_timing[2] = ev_ms(ev[1], ev[2]);
+  t_timing[3] = ev_ms(ev[2], ev[3]);
+  t_timing[4] = ev_ms(ev[3], ev[5]);
+  return 0;
+}
+
+// SCTL_B200_ALL_GPUS: contiguous target blocks [Nt*g/G, Nt*(g+1)/G) per visible device — the partition
+// formula of ParticleFMM::EvalDirect (fmm-wrapper.txx:507) — sources replicated by independent H2D
+// copies (they start on the host, so there is no collective), one host thread per device.
+static int eval_host_all_gpus(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                              const void* v_src, void* v_trg, int digits, bool accumulate) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+    cudaGetLastError();
+    return set_error(SCTL_B200_ERR_CUDA, "no usable CUDA device; libsctl_b200 has no CPU fallback");
+  }
+  if (ndev == 1 || Nt < ndev) return eval_host_one_device(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, v_src, v_trg, digits, accumulate);
+  int dev0 = 0;
+  CU_TRY(cudaGetDevice(&dev0));
+  const KernelInfo& ki = KINFO[kernel_id];
+  const size_t esz = elem_size(dtype);
+  std::vector<int> rcs(ndev, 0);
+  std::vector<std::string> msgs(ndev);
+  std::vector<std::thread> th;
+  for (int g = 0; g < ndev; g++) {
+    th.emplace_back([&, g]() {
+      if (cudaSetDevice(g) != cudaSuccess) {
+        rcs[g] = SCTL_B200_ERR_CUDA;
+        msgs[g] = "cudaSetDevice failed";
+        return;
+      }
+      const int64_t t0 = Nt * g / ndev, t1 = Nt * (g + 1) / ndev;
+      rcs[g] = eval_host_one_device(kernel_id, dtype, t1 - t0, Ns, (const char*)r_trg + (size_t)t0 * 3 * esz, r_src, n_src, v_src,
+                                    (char*)v_trg + (size_t)t0 * ki.trg_dim * esz, digits, accumulate);
+      if (rcs[g]) msgs[g] = t_last_error;
+    });
+  }
+  for (auto& t : th) t.join();
+  cudaSetDevice(dev0);
+  for (int g = 0; g < ndev; g++)
+    if (rcs[g]) return set_error(rcs[g], "device %d: %s", g, msgs[g].c_str());
+  return 0;
+}
+
+static int kmat_host(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src, void* M,
+                     int digits) {
+  DevCtx* c = nullptr;
+  int rc = get_ctx(&c);
+  if (rc) return rc;
+  if (Nt == 0 || Ns == 0) return 0;
+  const KernelInfo& ki = KINFO[kernel_id];
+  const size_t esz = elem_size(dtype);
+  cudaStream_t st = c->stream;
+  DevAlloc d_rt, d_rs, d_ns, d_M;
+  const size_t b_rt = (size_t)Nt * 3 * esz, b_rs = (size_t)Ns * 3 * esz, b_ns = (size_t)Ns * ki.normal_dim * esz;
+  const size_t row_bytes = (size_t)ki.src_dim * (size_t)Nt * ki.trg_dim * esz;  // bytes of M per source
+  // device slab of at most ~1 GiB of M at a time (rows of consecutive sources are contiguous in M)
+  int64_t slab = (int64_t)((1ull << 30) / (row_bytes ? row_bytes : 1));
+  if (slab < 1) slab = 1;
+  if (slab > Ns) slab = Ns;
+  if ((rc = d_rt.alloc(b_rt, st)) || (rc = d_rs.alloc(b_rs, st)) || (rc = d_ns.alloc(b_ns, st)) || (rc = d_M.alloc((size_t)slab * row_bytes, st)))
+    return rc;
+  cudaEvent_t* ev = c->ev;
+  CU_TRY(cudaEventRecord(ev[4], st));
+  CU_TRY(cudaMemcpyAsync(d_rt.p, r_trg, b_rt, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(d_rs.p, r_src, b_rs, cudaMemcpyHostToDevice, st));
+  if (b_ns) CU_TRY(cudaMemcpyAsync(d_ns.p, n_src, b_ns, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaEventRecord(ev[0], st));
+  for (int64_t s0 = 0; s0 < Ns; s0 += slab) {
+    const int64_t ns = Ns - s0 < slab ? Ns - s0 : slab;
+    rc = kmat_device(kernel_id, dtype, Nt, ns, d_rt.p, (const char*)d_rs.p + (size_t)s0 * 3 * esz,
+                     b_ns ? (const char*)d_ns.p + (size_t)s0 * ki.normal_dim * esz : nullptr, d_M.p, digits, st);
+    if (rc) return rc;
+    CU_TRY(cudaMemcpyAsync((char*)M + (size_t)s0 * row_bytes, d_M.p, (size_t)ns * row_bytes, cudaMemcpyDeviceToHost, st));
+  }
+  CU_TRY(cudaEventRecord(ev[5], st));
+  CU_TRY(cudaStreamSynchronize(st));
+  t_timing[0] = ev_ms(ev[4], ev[0]);
+  t_timing[1] = 0;
+  t_timing[2] = ev_ms(ev[0], ev[5]);
+  t_timing[3] = 0;
+  t_timing[4] = 0;
+  return 0;
+}
+
+}  // namespace sctl_b200
+
+using namespace sctl_b200;
+
+extern "C" {
+
+int sctl_b200_kernel_dims(int kernel_id, int* coord_dim, int* normal_dim, int* src_dim, int* trg_dim, double* scale, int* flops) {
+  if (kernel_id < 0 || kernel_id >= NUM_KERNELS) return set_error(SCTL_B200_ERR_KERNEL, "unknown kernel id %d", kernel_id);
+  const KernelInfo& ki = KINFO[kernel_id];
+  if (coord_dim) *coord_dim = 3;
+  if (normal_dim) *normal_dim = ki.normal_dim;
+  if (src_dim) *src_dim = ki.src_dim;
+  if (trg_dim) *trg_dim = ki.trg_dim;
+  if (scale) *scale = kernel_scale(kernel_id);
+  if (flops) *flops = ki.flops;
+  return 0;
+}
+
+const char* sctl_b200_kernel_name(int kernel_id) {
+  if (kernel_id < 0 || kernel_id >= NUM_KERNELS) return nullptr;
+  return KINFO[kernel_id].name;
+}
+
+int sctl_b200_eval(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                   const void* v_src, void* v_trg, int digits, unsigned flags) {
+  int rc = check_common(kernel_id, dtype, Nt, Ns);
+  if (rc) return rc;
+  const KernelInfo& ki = KINFO[kernel_id];
+  if ((Nt > 0 && (!r_trg || !v_trg)) || (Ns > 0 && Nt > 0 && (!r_src || !v_src || (ki.normal_dim && !n_src))))
+    return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if ((flags & SCTL_B200_DEVICE_PTRS) && (flags & SCTL_B200_ALL_GPUS))
+    return set_error(SCTL_B200_ERR_ARG, "SCTL_B200_ALL_GPUS needs host pointers");
+  const bool accumulate = !(flags & SCTL_B200_OVERWRITE);
+  if (flags & SCTL_B200_DEVICE_PTRS) {
+    DevCtx* c = nullptr;
+    if ((rc = get_ctx(&c))) return rc;
+    rc = eval_device(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, v_src, v_trg, digits, accumulate, c->stream, c->sms, nullptr);
+    if (rc) return rc;
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+  }
+  if (flags & SCTL_B200_ALL_GPUS) return eval_host_all_gpus(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, v_src, v_trg, digits, accumulate);
+  return eval_host_one_device(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, v_src, v_trg, digits, accumulate);
+}
+
+int sctl_b200_eval_async(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* d_r_trg, const void* d_r_src, const void* d_n_src,
+                         const void* d_v_src, void* d_v_trg, int digits, unsigned flags, void* cuda_stream) {
+  int rc = check_common(kernel_id, dtype, Nt, Ns);
+  if (rc) return rc;
+  const KernelInfo& ki = KINFO[kernel_id];
+  if ((Nt > 0 && (!d_r_trg || !d_v_trg)) || (Ns > 0 && Nt > 0 && (!d_r_src || !d_v_src || (ki.normal_dim && !d_n_src))))
+    return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if (flags & SCTL_B200_ALL_GPUS) return set_error(SCTL_B200_ERR_ARG, "SCTL_B200_ALL_GPUS needs host pointers");
+  DevCtx* c = nullptr;
+  if ((rc = get_ctx(&c))) return rc;
+  return eval_device(kernel_id, dtype, Nt, Ns, d_r_trg, d_r_src, d_n_src, d_v_src, d_v_trg, digits, !(flags & SCTL_B200_OVERWRITE),
+                     (cudaStream_t)cuda_stream, c->sms, nullptr);
+}
+
+int sctl_b200_kernel_matrix(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                            void* M, int digits, unsigned flags) {
+  int rc = check_common(kernel_id, dtype, Nt, Ns);
+  if (rc) return rc;
+  const KernelInfo& ki = KINFO[kernel_id];
+  if (Nt > 0 && Ns > 0 && (!r_trg || !r_src || !M || (ki.normal_dim && !n_src))) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if (flags & SCTL_B200_ALL_GPUS) return set_error(SCTL_B200_ERR_ARG, "SCTL_B200_ALL_GPUS is not supported for kernel_matrix");
+  if (flags & SCTL_B200_DEVICE_PTRS) {
+    DevCtx* c = nullptr;
+    if ((rc = get_ctx(&c))) return rc;
+    if ((rc = kmat_device(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, M, digits, c->stream))) return rc;
+    CU_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+  }
+  return kmat_host(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, M, digits);
+}
+
+int sctl_b200_kernel_matrix_async(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* d_r_trg, const void* d_r_src,
+                                  const void* d_n_src, void* d_M, int digits, unsigned flags, void* cuda_stream) {
+  int rc = check_common(kernel_id, dtype, Nt, Ns);
+  if (rc) return rc;
+  const KernelInfo& ki = KINFO[kernel_id];
+  if (Nt > 0 && Ns > 0 && (!d_r_trg || !d_r_src || !d_M || (ki.normal_dim && !d_n_src))) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if (flags & SCTL_B200_ALL_GPUS) return set_error(SCTL_B200_ERR_ARG, "SCTL_B200_ALL_GPUS is not supported for kernel_matrix");
+  DevCtx* c = nullptr;
+  if ((rc = get_ctx(&c))) return rc;
+  return kmat_device(kernel_id, dtype, Nt, Ns, d_r_trg, d_r_src, d_n_src, d_M, digits, (cudaStream_t)cuda_stream);
+}
+
+int sctl_b200_buf_create(void** d_ptr, int dtype, int64_t n) {
+  if (!d_ptr || n < 0) return set_error(SCTL_B200_ERR_ARG, "bad argument");
+  if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return set_error(SCTL_B200_ERR_DTYPE, "unknown dtype %d", dtype);
+  DevCtx* c = nullptr;
+  int rc = get_ctx(&c);
+  if (rc) return rc;
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, n ? (size_t)n * elem_size(dtype) : 16);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return set_error(SCTL_B200_ERR_NOMEM, "cudaMalloc: %s", cudaGetErrorString(e));
+  }
+  *d_ptr = p;
+  return 0;
+}
+int sctl_b200_buf_upload(void* d_ptr, const void* host, int dtype, int64_t n) {
+  if ((n > 0 && (!d_ptr || !host)) || n < 0) return set_error(SCTL_B200_ERR_ARG, "bad argument");
+  if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return set_error(SCTL_B200_ERR_DTYPE, "unknown dtype %d", dtype);
+  if (n) CU_TRY(cudaMemcpy(d_ptr, host, (size_t)n * elem_size(dtype), cudaMemcpyHostToDevice));
+  return 0;
+}
+int sctl_b200_buf_download(const void* d_ptr, void* host, int dtype, int64_t n) {
+  if ((n > 0 && (!d_ptr || !host)) || n < 0) return set_error(SCTL_B200_ERR_ARG, "bad argument");
+  if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return set_error(SCTL_B200_ERR_DTYPE, "unknown dtype %d", dtype);
+  if (n) CU_TRY(cudaMemcpy(host, d_ptr, (size_t)n * elem_size(dtype), cudaMemcpyDeviceToHost));
+  return 0;
+}
+int sctl_b200_buf_destroy(void* d_ptr) {
+  if (d_ptr) CU_TRY(cudaFree(d_ptr));
+  return 0;
+}
+
+int sctl_b200_device_count(int* n) {
+  if (!n) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  int c = 0;
+  cudaError_t e = cudaGetDeviceCount(&c);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    *n = 0;
+    return cuda_error(e, "cudaGetDeviceCount");
+  }
+  *n = c;
+  return 0;
+}
+int sctl_b200_set_device(int dev) {
+  CU_TRY(cudaSetDevice(dev));
+  return 0;
+}
+int sctl_b200_get_device(int* dev) {
+  if (!dev) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  CU_TRY(cudaGetDevice(dev));
+  return 0;
+}
+int sctl_b200_sm_count(int* n) {
+  if (!n) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  DevCtx* c = nullptr;
+  int rc = get_ctx(&c);
+  if (rc) return rc;
+  *n = c->sms;
+  return 0;
+}
+
+int64_t sctl_b200_launch_count(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
+
+int sctl_b200_measure_peak(int dtype, double seconds, double* tflops) {
+  if (!tflops) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return set_error(SCTL_B200_ERR_DTYPE, "unknown dtype %d", dtype);
+  DevCtx* c = nullptr;
+  int rc = get_ctx(&c);
+  if (rc) return rc;
+  CU_TRY(dtype == SCTL_B200_F64 ? run_peak_f64(seconds, tflops, c->stream) : run_peak_f32(seconds, tflops, c->stream));
+  return 0;
+}
+
+int sctl_b200_last_timing(double ms[5]) {
+  if (!ms) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  for (int i = 0; i < 5; i++) ms[i] = t_timing[i];
+  return 0;
+}
+
+const char* sctl_b200_last_error(void) { return t_last_error.c_str(); }
+const char* sctl_b200_version(void) { return "sctl_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,107 @@
+// Shared device helpers: mbarrier / 1-D bulk-TMA wrappers and the masked reciprocal square roots.
+// sm_100a only (cp.async.bulk + mbarrier expect_tx need sm_90+, the build passes -gencode arch=compute_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace sctl_b200 {
+
+// ---------------------------------------------------------------------------------------------
+// mbarrier + bulk async copy (TMA 1-D, SASS: UBLKCP) — PTX ISA "cp.async.bulk", "mbarrier".
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "LAB_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra LAB_DONE_%=;\n"
+      "bra LAB_WAIT_%=;\n"
+      "LAB_DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy, completion signalled on `bar` (bytes must be a multiple of 16, both
+// addresses 16-byte aligned).
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// rinv = (r2 > 0) ? 1/sqrt(r2) : 0      — the arithmetic of approx_rsqrt<digits>(r2, r2 > 0)
+// (reference: kernel_functions.hpp:28, vec.txx:361-364, intrin-wrapper.hpp:516-535,3025-3050).
+//
+// The reference refines a 14-bit hardware seed with 0/1/2 Newton steps chosen from `digits`.
+// Here the seed is MUFU.RSQ64H (PTX rsqrt.approx.ftz.f64: ~22 good bits, computed from the high
+// word only) and NEWTON selects the refinement on the FP64 pipe:
+//   NEWTON 0: seed only                       (rel. err ~2^-22  -> digits <= 6)
+//   NEWTON 1: one quadratic Newton step       (rel. err ~1.5*2^-44 -> digits <= 12), 3 FP64 ops
+//   NEWTON 2: one cubic (Halley-type) step    (rel. err ~1 ulp),  5 FP64 ops
+//       e = 1 - x*y0^2 ;  y1 = y0 * (1 + e/2 + 3e^2/8)     [1/sqrt(1-e) to second order]
+// The r2 == 0 mask is applied to the SEED with integer ops on the ALU pipe (as the reference masks
+// the seed, intrin-wrapper.hpp:3045), so masked lanes stay exactly 0 through the refinement and the
+// FP64 pipe sees no compare/select. Denormal r2 (< 2^-1022) is treated as 0, as .ftz does.
+// ---------------------------------------------------------------------------------------------
+template <int NEWTON>
+__device__ __forceinline__ double rsqrt_masked(double r2) {
+  double seed;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(seed) : "d"(r2));
+  const bool ok = __double2hiint(r2) >= 0x00100000;  // positive normal number
+  const int hi = ok ? __double2hiint(seed) : 0;
+  const double y0 = __hiloint2double(hi, 0);
+  if (NEWTON == 0) return y0;
+  const double t = r2 * y0;
+  const double e = fma(-t, y0, 1.0);
+  if (NEWTON == 1) {
+    // y0/2 by an exponent decrement on the integer pipe (y0 is normal or exactly 0 here)
+    const double h = __hiloint2double(ok ? hi - 0x00100000 : 0, 0);
+    return fma(h, e, y0);
+  }
+  const double p = fma(e, 0.375, 0.5);
+  const double q = e * p;
+  return fma(y0, q, y0);
+}
+
+// FP32: MUFU.RSQ (rsqrt.approx.ftz.f32, ~2^-22.4) + one Newton step for full precision, as the
+// reference's 1 iteration at digits = 6 (intrin-wrapper.hpp:3026).
+template <int NEWTON>
+__device__ __forceinline__ float rsqrt_masked(float r2) {
+  float seed;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"(r2));
+  const bool ok = __float_as_int(r2) >= 0x00800000;
+  const float y0 = ok ? seed : 0.0f;
+  if (NEWTON == 0) return y0;
+  const float t = r2 * y0;
+  const float e = fmaf(-t, y0, 1.0f);
+  const float h = 0.5f * y0;
+  return fmaf(h, e, y0);
+}
+
+template <class Real> struct VecOf;
+template <> struct VecOf<double> {
+  using type = double2;
+  static constexpr int N = 2;
+};
+template <> struct VecOf<float> {
+  using type = float4;
+  static constexpr int N = 4;
+};
+
+__host__ __device__ constexpr int round_up_int(int a, int b) { return (a + b - 1) / b * b; }
+
+}  // namespace sctl_b200

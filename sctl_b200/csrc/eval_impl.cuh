@@ -1,0 +1,237 @@
+// Direct summation kernels: pack -> eval (-> reduce).  Replaces the hot loop of
+// GenericKernel<uKernel>::Eval (reference: include/sctl/generic-kernel.txx:153-186).
+//
+// Mapping (B200-first, FP64/FP32 CUDA-core bound; no tensor cores — this is not a dense contraction):
+//   * the reference vectorises over TARGETS (SIMD lanes) and broadcasts each source
+//     (generic-kernel.txx:155-166). Here a thread owns R targets in registers (coordinates +
+//     accumulators), a CTA owns THREADS*R consecutive targets, and every source record is a
+//     warp-uniform shared-memory broadcast (LDS.128, conflict-free) reused by all R targets.
+//   * sources are first packed (pack_kernel) into records {x,y,z,payload} padded to the tile size with
+//     zero-density dummies, so the inner loop has no bounds checks and a tile is ONE contiguous block.
+//   * tiles are streamed global->shared by 1-D bulk TMA (cp.async.bulk, SASS UBLKCP) into a
+//     STAGES-deep ring guarded by full/empty mbarriers; thread 0 is the only producer.
+//   * grid = (target tiles) x (source chunks). Splitting the source range gives enough CTAs to kill
+//     wave quantisation when a GPU only holds a few hundred target tiles (8-GPU sharding) and for
+//     skinny problems (few targets, many sources). Chunk partial sums go to a [chunk][k][t] f64 buffer
+//     and a second tiny kernel adds them in a FIXED order -> results are run-to-run deterministic.
+//   * the scale factor is applied once after the sum and v_trg is accumulated into
+//     (generic-kernel.txx:182-186) by whichever kernel finishes the sum.
+//   * FP32: per-tile f32 accumulators are flushed into f64 accumulators after every tile so that
+//     16M-source sums stay inside 1e-5 (the reference accumulates in plain f32).
+#pragma once
+#include "ukernels.cuh"
+
+namespace sctl_b200 {
+
+constexpr int EVAL_THREADS = 128;  // 4 warps; 4 CTAs/SM at <=128 registers
+constexpr int EVAL_TILE = 256;     // sources per shared-memory stage
+constexpr int EVAL_STAGES = 2;
+
+struct EvalParams {
+  const void* r_trg;  // AoS [Nt*3]
+  const void* rec;    // packed source records [n_tiles*EVAL_TILE*REC]
+  void* v_trg;        // AoS [Nt*K1]                 (used when n_chunks == 1)
+  double* partial;    // [n_chunks][K1][nt_stride]   (used when n_chunks  > 1)
+  long long Nt;
+  long long nt_stride;
+  int n_tiles;          // total source tiles
+  int tiles_per_chunk;  // source tiles per blockIdx.y
+  int n_chunks;
+  int accumulate;  // v_trg += (1) or v_trg = (0)
+  double scale;
+};
+
+// ---------------------------------------------------------------------------------------------
+// pack: AoS (r_src, n_src, v_src) -> records {x,y,z,payload,0-pad}; tail padded with zero records
+// ---------------------------------------------------------------------------------------------
+template <class Ker, class Real>
+__global__ void __launch_bounds__(256) pack_kernel(const Real* __restrict__ r_src, const Real* __restrict__ n_src,
+                                                   const Real* __restrict__ v_src, Real* __restrict__ rec, long long Ns,
+                                                   long long Ns_pad) {
+  constexpr int REC = rec_len<Ker, Real>();
+  const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= Ns_pad) return;
+  Real out[REC];
+#pragma unroll
+  for (int i = 0; i < REC; i++) out[i] = (Real)0;
+  if (s < Ns) {
+    Real n[3] = {0, 0, 0}, f[Ker::K0];
+    out[0] = r_src[s * 3 + 0];
+    out[1] = r_src[s * 3 + 1];
+    out[2] = r_src[s * 3 + 2];
+#pragma unroll
+    for (int i = 0; i < Ker::ND; i++) n[i] = n_src[s * Ker::ND + i];
+#pragma unroll
+    for (int i = 0; i < Ker::K0; i++) f[i] = v_src[s * Ker::K0 + i];
+    Ker::pack(out + 3, n, f);
+  }
+  using V = typename VecOf<Real>::type;
+  V* dst = reinterpret_cast<V*>(rec + s * REC);
+#pragma unroll
+  for (int i = 0; i < REC / VecOf<Real>::N; i++) dst[i] = reinterpret_cast<const V*>(out)[i];
+}
+
+// ---------------------------------------------------------------------------------------------
+// eval: the O(Ns*Nt) kernel
+// ---------------------------------------------------------------------------------------------
+template <class Real> struct AccFlush;  // FP32 tiles are flushed into f64 accumulators
+template <> struct AccFlush<double> { static constexpr bool value = false; };
+template <> struct AccFlush<float> { static constexpr bool value = true; };
+
+template <class Ker, class Real, int R, int NEWTON, int MINB>
+__global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalParams p) {
+  constexpr int REC = rec_len<Ker, Real>();
+  constexpr int NACC = Ker::NACC;
+  constexpr int K1 = Ker::K1;
+  constexpr uint32_t TILE_BYTES = EVAL_TILE * REC * sizeof(Real);
+  using V = typename VecOf<Real>::type;
+  constexpr int NV = REC / VecOf<Real>::N;
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  Real* tiles = reinterpret_cast<Real*>(smem_raw);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_raw + (size_t)EVAL_STAGES * TILE_BYTES);
+  uint64_t* empty_bar = full_bar + EVAL_STAGES;
+
+  const int tid = threadIdx.x;
+  const int tile0 = blockIdx.y * p.tiles_per_chunk;
+  const int ntile = min(p.tiles_per_chunk, p.n_tiles - tile0);
+  const Real* rec = reinterpret_cast<const Real*>(p.rec) + (size_t)tile0 * EVAL_TILE * REC;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < EVAL_STAGES; s++) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], EVAL_THREADS / 32);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < EVAL_STAGES; s++) {
+      if (s < ntile) {
+        mbar_arrive_expect_tx(&full_bar[s], TILE_BYTES);
+        bulk_g2s(tiles + (size_t)s * EVAL_TILE * REC, rec + (size_t)s * EVAL_TILE * REC, TILE_BYTES, &full_bar[s]);
+      }
+    }
+  }
+
+  // R register-blocked targets per thread, strided by the CTA width so global accesses coalesce.
+  const long long t_base = (long long)blockIdx.x * (EVAL_THREADS * R) + tid;
+  const Real* r_trg = reinterpret_cast<const Real*>(p.r_trg);
+  Real xt[R], yt[R], zt[R];
+  Real acc[R][NACC];
+  double acc64[AccFlush<Real>::value ? R : 1][NACC];
+#pragma unroll
+  for (int r = 0; r < R; r++) {
+    long long t = t_base + (long long)r * EVAL_THREADS;
+    t = t < p.Nt ? t : p.Nt - 1;  // clamp: out-of-range lanes recompute the last target and are not stored
+    xt[r] = r_trg[t * 3 + 0];
+    yt[r] = r_trg[t * 3 + 1];
+    zt[r] = r_trg[t * 3 + 2];
+#pragma unroll
+    for (int k = 0; k < NACC; k++) {
+      acc[r][k] = (Real)0;
+      if (AccFlush<Real>::value) acc64[r][k] = 0.0;
+    }
+  }
+
+  for (int k = 0; k < ntile; k++) {
+    const int stage = k % EVAL_STAGES;
+    const uint32_t parity = (uint32_t)(k / EVAL_STAGES) & 1u;
+    mbar_wait(&full_bar[stage], parity);
+    const V* tile = reinterpret_cast<const V*>(tiles + (size_t)stage * EVAL_TILE * REC);
+
+#pragma unroll 2
+    for (int s = 0; s < EVAL_TILE; s++) {
+      Real src[REC];
+#pragma unroll
+      for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];  // warp-uniform LDS.128 broadcast
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const Real dx = xt[r] - src[0];
+        const Real dy = yt[r] - src[1];
+        const Real dz = zt[r] - src[2];
+        Real r2 = dx * dx;
+        r2 = fma(dy, dy, r2);
+        r2 = fma(dz, dz, r2);
+        const Real rinv = rsqrt_masked<NEWTON>(r2);
+        Ker::apply(acc[r], dx, dy, dz, rinv, src + 3);
+      }
+    }
+
+    if (AccFlush<Real>::value) {
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+#pragma unroll
+        for (int q = 0; q < NACC; q++) {
+          acc64[r][q] += (double)acc[r][q];
+          acc[r][q] = (Real)0;
+        }
+      }
+    }
+
+    // release the stage; thread 0 refills it with tile k+STAGES once every warp has released it
+    __syncwarp();
+    if ((tid & 31) == 0) mbar_arrive(&empty_bar[stage]);
+    if (tid == 0 && k + EVAL_STAGES < ntile) {
+      mbar_wait(&empty_bar[stage], parity);
+      mbar_arrive_expect_tx(&full_bar[stage], TILE_BYTES);
+      bulk_g2s(tiles + (size_t)stage * EVAL_TILE * REC, rec + (size_t)(k + EVAL_STAGES) * EVAL_TILE * REC, TILE_BYTES,
+               &full_bar[stage]);
+    }
+    __syncwarp();
+  }
+
+  // epilogue
+#pragma unroll
+  for (int r = 0; r < R; r++) {
+    const long long t = t_base + (long long)r * EVAL_THREADS;
+    if (t >= p.Nt) continue;
+    double a[NACC], out[K1];
+#pragma unroll
+    for (int q = 0; q < NACC; q++) a[q] = AccFlush<Real>::value ? acc64[r][q] : (double)acc[r][q];
+    Ker::finalize(out, a);
+    if (p.n_chunks == 1) {
+      Real* v = reinterpret_cast<Real*>(p.v_trg) + t * K1;
+#pragma unroll
+      for (int q = 0; q < K1; q++) {
+        const double prev = p.accumulate ? (double)v[q] : 0.0;
+        v[q] = (Real)(prev + out[q] * p.scale);
+      }
+    } else {
+      double* dst = p.partial + (size_t)blockIdx.y * K1 * p.nt_stride + t;
+#pragma unroll
+      for (int q = 0; q < K1; q++) dst[(size_t)q * p.nt_stride] = out[q];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// reduce: v_trg[t*K1+k] (+)= scale * sum_c partial[c][k][t]   (fixed chunk order -> deterministic)
+// ---------------------------------------------------------------------------------------------
+template <class Real, int K1>
+__global__ void __launch_bounds__(256) reduce_kernel(const double* __restrict__ partial, Real* __restrict__ v_trg, long long Nt,
+                                                     long long nt_stride, int n_chunks, double scale, int accumulate) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= Nt) return;
+  double sum[K1];
+#pragma unroll
+  for (int q = 0; q < K1; q++) sum[q] = 0.0;
+  for (int c = 0; c < n_chunks; c++) {
+#pragma unroll
+    for (int q = 0; q < K1; q++) sum[q] += partial[((size_t)c * K1 + q) * nt_stride + t];
+  }
+#pragma unroll
+  for (int q = 0; q < K1; q++) {
+    const double prev = accumulate ? (double)v_trg[t * K1 + q] : 0.0;
+    v_trg[t * K1 + q] = (Real)(prev + sum[q] * scale);
+  }
+}
+
+template <class Ker, class Real>
+constexpr size_t eval_smem_bytes() {
+  return (size_t)EVAL_STAGES * EVAL_TILE * rec_len<Ker, Real>() * sizeof(Real) + 2 * EVAL_STAGES * sizeof(uint64_t);
+}
+
+}  // namespace sctl_b200

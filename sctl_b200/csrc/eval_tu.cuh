@@ -1,0 +1,113 @@
+// Included by eval_f64.cu / eval_f32.cu with SCTL_B200_REAL and SCTL_B200_TABLE_FN defined:
+// instantiates pack/eval/reduce/kmat for all eight micro-kernels and fills the launch table.
+#include "kmat_impl.cuh"
+#include "launch.h"
+
+namespace sctl_b200 {
+namespace {
+
+using Real = SCTL_B200_REAL;
+constexpr int RBIG = 4;    // throughput variant
+constexpr int RSMALL = 1;  // small-Nt variant
+constexpr bool IS_F32 = sizeof(Real) == 4;
+
+template <class Ker>
+cudaError_t pack_t(const void* r_src, const void* n_src, const void* v_src, void* rec, long long Ns, long long Ns_pad, cudaStream_t st) {
+  const unsigned blocks = (unsigned)((Ns_pad + 255) / 256);
+  pack_kernel<Ker, Real><<<blocks, 256, 0, st>>>((const Real*)r_src, (const Real*)n_src, (const Real*)v_src, (Real*)rec, Ns, Ns_pad);
+  count_launch();
+  return cudaGetLastError();
+}
+
+template <int R> constexpr int minb_for() { return R >= 4 ? 4 : 8; }
+
+template <class Ker, int R, int NEWTON>
+cudaError_t eval_t(const EvalParams& p, long long n_ttiles, cudaStream_t st) {
+  auto kern = eval_kernel<Ker, Real, R, NEWTON, minb_for<R>()>;
+  constexpr size_t smem = eval_smem_bytes<Ker, Real>();
+  static thread_local int attr_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr_dev != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_dev = dev;
+  }
+  dim3 grid((unsigned)n_ttiles, (unsigned)p.n_chunks, 1);
+  kern<<<grid, EVAL_THREADS, smem, st>>>(p);
+  count_launch();
+  return cudaGetLastError();
+}
+
+template <class Ker, int R, int NEWTON>
+int occ_t() {
+  auto kern = eval_kernel<Ker, Real, R, NEWTON, minb_for<R>()>;
+  constexpr size_t smem = eval_smem_bytes<Ker, Real>();
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, EVAL_THREADS, smem) != cudaSuccess || n < 1) n = 1;
+  return n;
+}
+
+template <class Ker>
+cudaError_t reduce_t(const double* partial, void* v_trg, long long Nt, long long nt_stride, int n_chunks, double scale, int accumulate,
+                     cudaStream_t st) {
+  const unsigned blocks = (unsigned)((Nt + 255) / 256);
+  reduce_kernel<Real, Ker::K1><<<blocks, 256, 0, st>>>(partial, (Real*)v_trg, Nt, nt_stride, n_chunks, scale, accumulate);
+  count_launch();
+  return cudaGetLastError();
+}
+
+template <class Ker, int NEWTON>
+cudaError_t kmat_t(const void* r_trg, const void* r_src, const void* n_src, void* M, long long Nt, long long Ns, double scale, cudaStream_t st) {
+  const long long gx = (Nt + KMAT_THREADS - 1) / KMAT_THREADS;
+  const long long gy = (Ns + KMAT_SB - 1) / KMAT_SB;
+  if (gy > 65535) return cudaErrorInvalidValue;  // callers slab the source range
+  dim3 grid((unsigned)gx, (unsigned)gy, 1);
+  kmat_kernel<Ker, Real, NEWTON><<<grid, KMAT_THREADS, 0, st>>>((const Real*)r_trg, (const Real*)r_src, (const Real*)n_src, (Real*)M, Nt, Ns,
+                                                             (Real)scale);
+  count_launch();
+  return cudaGetLastError();
+}
+
+template <class Ker>
+EvalEntry make_entry() {
+  EvalEntry e{};
+  e.rec_len = rec_len<Ker, Real>();
+  e.k0 = Ker::K0;
+  e.k1 = Ker::K1;
+  e.nd = Ker::ND;
+  e.R[0] = RSMALL;
+  e.R[1] = RBIG;
+  e.pack = pack_t<Ker>;
+  e.reduce = reduce_t<Ker>;
+  // f32 has refinement levels 0 and 1 only; level 2 aliases level 1
+  e.eval[0][0] = eval_t<Ker, RSMALL, 0>;
+  e.eval[0][1] = eval_t<Ker, RSMALL, 1>;
+  e.eval[0][2] = eval_t<Ker, RSMALL, IS_F32 ? 1 : 2>;
+  e.eval[1][0] = eval_t<Ker, RBIG, 0>;
+  e.eval[1][1] = eval_t<Ker, RBIG, 1>;
+  e.eval[1][2] = eval_t<Ker, RBIG, IS_F32 ? 1 : 2>;
+  e.occupancy[0][0] = occ_t<Ker, RSMALL, 0>;
+  e.occupancy[0][1] = occ_t<Ker, RSMALL, 1>;
+  e.occupancy[0][2] = occ_t<Ker, RSMALL, IS_F32 ? 1 : 2>;
+  e.occupancy[1][0] = occ_t<Ker, RBIG, 0>;
+  e.occupancy[1][1] = occ_t<Ker, RBIG, 1>;
+  e.occupancy[1][2] = occ_t<Ker, RBIG, IS_F32 ? 1 : 2>;
+  e.kmat[0] = kmat_t<Ker, 0>;
+  e.kmat[1] = kmat_t<Ker, 1>;
+  e.kmat[2] = kmat_t<Ker, IS_F32 ? 1 : 2>;
+  return e;
+}
+
+}  // namespace
+
+const EvalEntry* SCTL_B200_TABLE_FN() {
+  static const EvalEntry table[NUM_KERNELS] = {
+      make_entry<KLaplaceFxU>(), make_entry<KLaplaceDxU>(), make_entry<KLaplaceFxdU>(), make_entry<KStokesFxU>(),
+      make_entry<KStokesDxU>(),  make_entry<KStokesFxT>(),  make_entry<KStokesFSxU>(),  make_entry<KStokesFxUP>(),
+  };
+  return table;
+}
+
+}  // namespace sctl_b200

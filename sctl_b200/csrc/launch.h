@@ -1,0 +1,38 @@
+// Host-side launch tables shared between the translation units of libsctl_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "eval_impl.cuh"
+#include "kmat_impl.cuh"
+
+namespace sctl_b200 {
+
+constexpr int NUM_KERNELS = 8;
+constexpr int NUM_RVAR = 2;    // register-blocking variants: [0] = small-Nt (R=1), [1] = throughput (R=4)
+constexpr int NUM_NEWTON = 3;  // rsqrt refinement levels (f32 uses 0..1)
+
+struct EvalEntry {
+  int rec_len;  // Reals per packed source record
+  int k0, k1, nd;
+  int R[NUM_RVAR];
+  cudaError_t (*pack)(const void* r_src, const void* n_src, const void* v_src, void* rec, long long Ns, long long Ns_pad, cudaStream_t st);
+  // launches grid (n_ttiles, p.n_chunks)
+  cudaError_t (*eval[NUM_RVAR][NUM_NEWTON])(const EvalParams& p, long long n_ttiles, cudaStream_t st);
+  // resident CTAs per SM for that instantiation (queried once)
+  int (*occupancy[NUM_RVAR][NUM_NEWTON])();
+  cudaError_t (*reduce)(const double* partial, void* v_trg, long long Nt, long long nt_stride, int n_chunks, double scale, int accumulate,
+                        cudaStream_t st);
+  cudaError_t (*kmat[NUM_NEWTON])(const void* r_trg, const void* r_src, const void* n_src, void* M, long long Nt, long long Ns, double scale,
+                                  cudaStream_t st);
+};
+
+const EvalEntry* eval_table_f64();  // [NUM_KERNELS]
+const EvalEntry* eval_table_f32();
+
+void count_launch(int n = 1);
+
+// peak.cu
+cudaError_t run_peak_f64(double seconds, double* tflops, cudaStream_t st);
+cudaError_t run_peak_f32(double seconds, double* tflops, cudaStream_t st);
+
+}  // namespace sctl_b200

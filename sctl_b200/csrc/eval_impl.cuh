@@ -9,7 +9,7 @@
 //   * sources are first packed (pack_kernel) into records {x,y,z,payload} padded to the tile size with
 //     zero-density dummies, so the inner loop has no bounds checks and a tile is ONE contiguous block.
 //   * tiles are streamed global->shared by 1-D bulk TMA (cp.async.bulk, SASS UBLKCP) into a
-//     STAGES-deep ring guarded by full/empty mbarriers; thread 0 is the only producer.
+//     STAGES-deep ring guarded by full/empty mbarriers; warp 0 doubles as the producer.
 //   * grid = (target tiles) x (source chunks). Splitting the source range gives enough CTAs to kill
 //     wave quantisation when a GPU only holds a few hundred target tiles (8-GPU sharding) and for
 //     skinny problems (few targets, many sources). Chunk partial sums go to a [chunk][k][t] f64 buffer
@@ -24,8 +24,8 @@
 namespace sctl_b200 {
 
 constexpr int EVAL_THREADS = 128;  // 4 warps; 4 CTAs/SM at <=128 registers
-constexpr int EVAL_TILE = 256;     // sources per shared-memory stage
-constexpr int EVAL_STAGES = 2;
+constexpr int EVAL_TILE = 128;     // sources per shared-memory stage
+constexpr int EVAL_STAGES = 4;     // ring depth (tile k-1's slot is refilled while tile k is consumed)
 
 struct EvalParams {
   const void* r_trg;  // AoS [Nt*3]
@@ -171,16 +171,22 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
       }
     }
 
-    // release the stage; thread 0 refills it with tile k+STAGES once every warp has released it
+    // Release the stage. Warp 0 then refills the slot that tile k-1 used (released by every warp about one
+    // tile ago, so the wait below practically never blocks) with tile k-1+STAGES. All 32 lanes of warp 0
+    // poll the barrier together — a lane-0-only wait would leave the warp diverged for the whole next tile —
+    // and a single lane issues the copy.
     __syncwarp();
     if ((tid & 31) == 0) mbar_arrive(&empty_bar[stage]);
-    if (tid == 0 && k + EVAL_STAGES < ntile) {
-      mbar_wait(&empty_bar[stage], parity);
-      mbar_arrive_expect_tx(&full_bar[stage], TILE_BYTES);
-      bulk_g2s(tiles + (size_t)stage * EVAL_TILE * REC, rec + (size_t)(k + EVAL_STAGES) * EVAL_TILE * REC, TILE_BYTES,
-               &full_bar[stage]);
+    if (tid < 32 && k >= 1 && k - 1 + EVAL_STAGES < ntile) {
+      const int j = k - 1;
+      const int js = j % EVAL_STAGES;
+      mbar_wait(&empty_bar[js], (uint32_t)(j / EVAL_STAGES) & 1u);
+      if (tid == 0) {
+        mbar_arrive_expect_tx(&full_bar[js], TILE_BYTES);
+        bulk_g2s(tiles + (size_t)js * EVAL_TILE * REC, rec + (size_t)(j + EVAL_STAGES) * EVAL_TILE * REC, TILE_BYTES, &full_bar[js]);
+      }
+      __syncwarp();
     }
-    __syncwarp();
   }
 
   // epilogue

@@ -1,0 +1,40 @@
+"""The reference-side binding (include/sctl_b200/generic-kernel-b200.hpp) exercised by the reference's own C++ call
+sites: tests/cpp/shim_test is compiled against the UNMODIFIED reference headers where /root/reference exists (the
+authoring container, by __graft_entry__.build()) and travels to the GPU box as a built file."""
+import os
+import subprocess
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+BINS = [os.path.join(HERE, "cpp", "shim_test"), os.path.join(HERE, "cpp", "shim_test_memdebug")]
+
+
+def _need(path):
+    if not os.path.exists(path):
+        pytest.skip(f"{os.path.basename(path)} not built (needs /root/reference; run __graft_entry__.build())")
+
+
+@pytest.mark.parametrize("path", BINS, ids=["plain", "memdebug"])
+def test_shim_fails_loudly_without_gpu(path):
+    """no CPU fallback: without a usable device the reference's Eval must abort through SCTL_ERROR (common.hpp:53-70)"""
+    _need(path)
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present; the loud-failure path is checked on the CPU box")
+    p = subprocess.run([path, "--no-gpu"], capture_output=True, text=True, timeout=120)
+    assert p.returncode != 0, p.stdout
+    assert "no CPU fallback" in (p.stderr + p.stdout)
+    assert "UNEXPECTED" not in p.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", BINS, ids=["plain", "memdebug"])
+def test_shim_matches_reference_cpu_templates(path):
+    """all 8 kernels x f32/f64: Eval, accumulate, type-erased static Eval, KernelMatrix shapes, ParticleFMM::EvalDirect"""
+    _need(path)
+    p = subprocess.run([path], capture_output=True, text=True, timeout=900)
+    print(p.stdout[-6000:])
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
+    assert "SHIM TEST PASSED" in p.stdout

@@ -52,19 +52,19 @@
 
 namespace sctl_b200_shim {
 
-template <class uKernel> struct KernelId;  // kernel_functions.hpp struct -> id of sctl_b200.h
-template <> struct KernelId<sctl::kernel_impl::Laplace3D_FxU> { static constexpr int value = SCTL_B200_LAPLACE3D_FXU; };
-template <> struct KernelId<sctl::kernel_impl::Laplace3D_DxU> { static constexpr int value = SCTL_B200_LAPLACE3D_DXU; };
-template <> struct KernelId<sctl::kernel_impl::Laplace3D_FxdU> { static constexpr int value = SCTL_B200_LAPLACE3D_FXDU; };
-template <> struct KernelId<sctl::kernel_impl::Stokes3D_FxU> { static constexpr int value = SCTL_B200_STOKES3D_FXU; };
-template <> struct KernelId<sctl::kernel_impl::Stokes3D_DxU> { static constexpr int value = SCTL_B200_STOKES3D_DXU; };
-template <> struct KernelId<sctl::kernel_impl::Stokes3D_FxT> { static constexpr int value = SCTL_B200_STOKES3D_FXT; };
-template <> struct KernelId<sctl::kernel_impl::Stokes3D_FSxU> { static constexpr int value = SCTL_B200_STOKES3D_FSXU; };
-template <> struct KernelId<sctl::kernel_impl::Stokes3D_FxUP> { static constexpr int value = SCTL_B200_STOKES3D_FXUP; };
+template <class uKernel> struct KernelId { static constexpr bool known = false; };  // kernel_functions.hpp struct -> id of sctl_b200.h
+template <> struct KernelId<sctl::kernel_impl::Laplace3D_FxU> { static constexpr bool known = true; static constexpr int value = SCTL_B200_LAPLACE3D_FXU; };
+template <> struct KernelId<sctl::kernel_impl::Laplace3D_DxU> { static constexpr bool known = true; static constexpr int value = SCTL_B200_LAPLACE3D_DXU; };
+template <> struct KernelId<sctl::kernel_impl::Laplace3D_FxdU> { static constexpr bool known = true; static constexpr int value = SCTL_B200_LAPLACE3D_FXDU; };
+template <> struct KernelId<sctl::kernel_impl::Stokes3D_FxU> { static constexpr bool known = true; static constexpr int value = SCTL_B200_STOKES3D_FXU; };
+template <> struct KernelId<sctl::kernel_impl::Stokes3D_DxU> { static constexpr bool known = true; static constexpr int value = SCTL_B200_STOKES3D_DXU; };
+template <> struct KernelId<sctl::kernel_impl::Stokes3D_FxT> { static constexpr bool known = true; static constexpr int value = SCTL_B200_STOKES3D_FXT; };
+template <> struct KernelId<sctl::kernel_impl::Stokes3D_FSxU> { static constexpr bool known = true; static constexpr int value = SCTL_B200_STOKES3D_FSXU; };
+template <> struct KernelId<sctl::kernel_impl::Stokes3D_FxUP> { static constexpr bool known = true; static constexpr int value = SCTL_B200_STOKES3D_FXUP; };
 
 template <class Real> struct DType;
-template <> struct DType<float> { static constexpr int value = SCTL_B200_F32; };
-template <> struct DType<double> { static constexpr int value = SCTL_B200_F64; };
+template <> struct DType<float> { static constexpr bool known = true; static constexpr int value = SCTL_B200_F32; };
+template <> struct DType<double> { static constexpr bool known = true; static constexpr int value = SCTL_B200_F64; };
 
 template <class Real> inline const Real* cptr(const sctl::Vector<Real>& v) { return v.Dim() ? &v[0] : nullptr; }
 template <class Real> inline Real* mptr(sctl::Vector<Real>& v) { return v.Dim() ? &v[0] : nullptr; }

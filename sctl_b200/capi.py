@@ -10,7 +10,8 @@ import ctypes
 import os
 from ctypes import POINTER, c_char_p, c_double, c_int, c_int64, c_uint, c_void_p
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libsctl_b200.so")
+# SCTL_B200_LIB selects another build of the SAME library (tuning variants under sctl_b200/lib/variants); there is no other backend
+LIB_PATH = os.environ.get("SCTL_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libsctl_b200.so")
 
 # enums of include/sctl_b200.h
 F32, F64 = 0, 1

@@ -23,9 +23,23 @@
 
 namespace sctl_b200 {
 
-constexpr int EVAL_THREADS = 128;  // 4 warps; 4 CTAs/SM at <=128 registers
-constexpr int EVAL_TILE = 128;     // sources per shared-memory stage
-constexpr int EVAL_STAGES = 4;     // ring depth (tile k-1's slot is refilled while tile k is consumed)
+// Tuning knobs (compile-time; the -D overrides exist for the variant sweeps of scripts/build_variants.sh)
+#ifndef SCTL_B200_EVAL_THREADS
+#define SCTL_B200_EVAL_THREADS 128
+#endif
+#ifndef SCTL_B200_EVAL_TILE
+#define SCTL_B200_EVAL_TILE 128
+#endif
+#ifndef SCTL_B200_EVAL_STAGES
+#define SCTL_B200_EVAL_STAGES 4
+#endif
+#ifndef SCTL_B200_UNROLL
+#define SCTL_B200_UNROLL 2
+#endif
+constexpr int EVAL_THREADS = SCTL_B200_EVAL_THREADS;  // 4 warps; 4 CTAs/SM at <=128 registers
+constexpr int EVAL_TILE = SCTL_B200_EVAL_TILE;        // sources per shared-memory stage
+constexpr int EVAL_STAGES = SCTL_B200_EVAL_STAGES;    // ring depth (tile k-1's slot is refilled while tile k is consumed)
+constexpr int EVAL_UNROLL = SCTL_B200_UNROLL;         // source-loop unroll factor
 
 struct EvalParams {
   const void* r_trg;  // AoS [Nt*3]
@@ -142,7 +156,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
     mbar_wait(&full_bar[stage], parity);
     const V* tile = reinterpret_cast<const V*>(tiles + (size_t)stage * EVAL_TILE * REC);
 
-#pragma unroll 2
+#pragma unroll EVAL_UNROLL
     for (int s = 0; s < EVAL_TILE; s++) {
       Real src[REC];
 #pragma unroll

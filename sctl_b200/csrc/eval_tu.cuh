@@ -7,8 +7,17 @@ namespace sctl_b200 {
 namespace {
 
 using Real = SCTL_B200_REAL;
-constexpr int RBIG = 4;    // throughput variant
-constexpr int RSMALL = 1;  // small-Nt variant
+#ifndef SCTL_B200_RBIG
+#define SCTL_B200_RBIG 4
+#endif
+#ifndef SCTL_B200_MINB_BIG
+#define SCTL_B200_MINB_BIG 4
+#endif
+#ifndef SCTL_B200_ONLY_KERNEL
+#define SCTL_B200_ONLY_KERNEL -1  // >= 0: instantiate only that kernel id (fast variant builds for tuning sweeps)
+#endif
+constexpr int RBIG = SCTL_B200_RBIG;  // throughput variant
+constexpr int RSMALL = 1;             // small-Nt variant
 constexpr bool IS_F32 = sizeof(Real) == 4;
 
 template <class Ker>
@@ -19,7 +28,7 @@ cudaError_t pack_t(const void* r_src, const void* n_src, const void* v_src, void
   return cudaGetLastError();
 }
 
-template <int R> constexpr int minb_for() { return R >= 4 ? 4 : 8; }
+template <int R> constexpr int minb_for() { return R == RBIG ? SCTL_B200_MINB_BIG : 8; }
 
 template <class Ker, int R, int NEWTON>
 cudaError_t eval_t(const EvalParams& p, long long n_ttiles, cudaStream_t st) {
@@ -70,9 +79,12 @@ cudaError_t kmat_t(const void* r_trg, const void* r_src, const void* n_src, void
   return cudaGetLastError();
 }
 
-template <class Ker>
+template <class Ker, int ID>
 EvalEntry make_entry() {
   EvalEntry e{};
+  if constexpr (SCTL_B200_ONLY_KERNEL >= 0 && SCTL_B200_ONLY_KERNEL != ID) {
+    return e;
+  } else {
   e.rec_len = rec_len<Ker, Real>();
   e.k0 = Ker::K0;
   e.k1 = Ker::K1;
@@ -98,14 +110,15 @@ EvalEntry make_entry() {
   e.kmat[1] = kmat_t<Ker, 1>;
   e.kmat[2] = kmat_t<Ker, IS_F32 ? 1 : 2>;
   return e;
+  }
 }
 
 }  // namespace
 
 const EvalEntry* SCTL_B200_TABLE_FN() {
   static const EvalEntry table[NUM_KERNELS] = {
-      make_entry<KLaplaceFxU>(), make_entry<KLaplaceDxU>(), make_entry<KLaplaceFxdU>(), make_entry<KStokesFxU>(),
-      make_entry<KStokesDxU>(),  make_entry<KStokesFxT>(),  make_entry<KStokesFSxU>(),  make_entry<KStokesFxUP>(),
+      make_entry<KLaplaceFxU, 0>(), make_entry<KLaplaceDxU, 1>(), make_entry<KLaplaceFxdU, 2>(), make_entry<KStokesFxU, 3>(),
+      make_entry<KStokesDxU, 4>(),  make_entry<KStokesFxT, 5>(),  make_entry<KStokesFSxU, 6>(),  make_entry<KStokesFxUP, 7>(),
   };
   return table;
 }

@@ -1,0 +1,93 @@
+"""BASELINE.json's configs at their FULL sizes, on the GPU, through the device-pointer C-ABI entry. The CPU checker
+cannot sweep 1e12-1e14 pairs, so parity is checked (i) exactly as SURVEY.md 8(c) prescribes — a fixed random subset of
+targets against ALL sources with the reference's own Eval — and (ii) through size-independent properties of the sum:
+additivity over a split of the source range (Eval accumulates, generic-kernel.txx:98-101) and linearity in the density.
+
+  C2  Laplace3D_FxU, Laplace3D_FxdU   1M x 1M   f64
+  C3  Stokes3D_FxU                    4M x 4M   f64
+  C4  Laplace3D_DxU, Stokes3D_DxU     2M x 2M   f64
+  C5  Stokes3D_FxU                    16M sources x one rank's 2M-target shard of the 16M targets (8-GPU config), f32,
+                                      checked against the f64 reference (north_star: <= 1e-5)
+"""
+import numpy as np
+import pytest
+
+from sctl_b200 import KERNELS, capi, synth
+from util import TOL, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+N_CHECK = 48  # targets compared with the CPU checker (x all sources)
+
+
+def _dev(a):
+    import torch
+
+    return None if a is None else torch.from_numpy(a).cuda()
+
+
+def _subset_check(checker, kid, Xt, Xs, Xn, F, U, tol, seed=7):
+    """rel-L2 over a fixed random subset of targets; the checker runs in f64 on the (possibly f32) inputs"""
+    d = capi.kernel_dims(kid)
+    Nt = Xt.size // 3
+    rng = np.random.default_rng(seed)
+    idx = np.unique(np.concatenate([rng.integers(0, Nt, N_CHECK - 4), [0, 1, Nt - 2, Nt - 1]]))  # incl. coincident + last tile
+    f64 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+    xt = f64(Xt.reshape(-1, 3)[idx].reshape(-1))
+    want = checker.eval(kid, xt, f64(Xs), f64(Xn), f64(F)).reshape(-1, d["trg_dim"])
+    got = U.reshape(-1, d["trg_dim"])[idx]
+    err = rel_l2(got, want)
+    assert np.all(np.isfinite(got))
+    assert err <= tol, f"{d['name']}: rel-L2 {err:.3e} over {idx.size} targets x {Xs.size // 3} sources"
+    return err
+
+
+@pytest.mark.parametrize("kid,N,dt", [(0, 1_000_000, np.float64), (2, 1_000_000, np.float64),  # C2
+                                      (3, 4_000_000, np.float64),                              # C3
+                                      (1, 2_000_000, np.float64), (4, 2_000_000, np.float64)], # C4
+                         ids=["C2-Laplace_FxU-1M", "C2-Laplace_FxdU-1M", "C3-Stokes_FxU-4M", "C4-Laplace_DxU-2M", "C4-Stokes_DxU-2M"])
+def test_full_size_f64(checker, kid, N, dt):
+    import torch
+
+    d = capi.kernel_dims(kid)
+    ker = KERNELS[kid]()
+    Xt, Xs, Xn, F = synth.make_problem(d, N, N, dt)
+    dXt, dXs, dXn, dF = _dev(Xt), _dev(Xs), _dev(Xn), _dev(F)
+    U = ker.Eval(None, dXt, dXs, dXn, dF)
+    torch.cuda.synchronize()
+    Uh = U.cpu().numpy()
+    _subset_check(checker, kid, Xt, Xs, Xn, F, Uh, TOL[np.dtype(dt)])
+
+    # properties on a 256k-target slab x ALL sources (cheap: ~1e12 pairs)
+    T = 262_144
+    K0, K1, Nd = d["src_dim"], d["trg_dim"], d["normal_dim"]
+    xt = dXt[: 3 * T]
+    full = U[: K1 * T]
+    # additivity over a ragged split of the source range, second half ACCUMULATED into the first
+    h = N // 2 + 77
+    part = ker.Eval(None, xt, dXs[: 3 * h], dXn[: Nd * h] if Nd else None, dF[: K0 * h], overwrite=True)
+    part = ker.Eval(part, xt, dXs[3 * h:], dXn[Nd * h:] if Nd else None, dF[K0 * h:])
+    torch.cuda.synchronize()
+    assert rel_l2(part.cpu().numpy(), full.cpu().numpy()) <= 1e-13
+    # linearity in the density: K[a F + G] = a K[F] + K[G]
+    G = _dev(synth.uniform(11, 0, K0 * N, dtype=dt))
+    UG = ker.Eval(None, xt, dXs, dXn, G)
+    UFG = ker.Eval(None, xt, dXs, dXn, 0.75 * dF + G)
+    torch.cuda.synchronize()
+    assert rel_l2(UFG.cpu().numpy(), (0.75 * full + UG).cpu().numpy()) <= 1e-12
+
+
+def test_full_size_f32_16M_sources(checker):
+    """C5: FP32 accumulation over 16M sources must stay within 1e-5 of the f64 reference (per-tile f32 partial sums are
+    flushed into f64 accumulators in the kernel; the reference itself accumulates in plain f32)."""
+    import torch
+
+    kid, Ns, Nt_total, ranks = 3, 16_000_000, 16_000_000, 8
+    d = capi.kernel_dims(kid)
+    t0, t1 = 0, Nt_total // ranks  # rank 0's target block (fmm-wrapper.txx:507); it holds the coincident points
+    Xt, Xs, Xn, F = synth.make_problem(d, Nt_total, Ns, np.float32, t0=t0, t1=t1)
+    ker = KERNELS[kid]()
+    U = ker.Eval(None, _dev(Xt), _dev(Xs), None, _dev(F))
+    torch.cuda.synchronize()
+    err = _subset_check(checker, kid, Xt, Xs, Xn, F, U.cpu().numpy(), 1e-5)
+    print(f"C5 f32 16M sources: rel-L2 vs f64 reference = {err:.3e}")

@@ -22,6 +22,9 @@ for v in "$@"; do
     u1) build u1 -DSCTL_B200_UNROLL=1 ;;
     u4) build u4 -DSCTL_B200_UNROLL=4 ;;
     tile256) build tile256 -DSCTL_B200_EVAL_TILE=256 ;;
+    custom:*) # custom:name:R:MINB:THREADS:UNROLL[:TILE[:STAGES]]
+      IFS=: read -r _ n R M T U TL ST <<< "$v"
+      build $n -DSCTL_B200_RBIG=$R -DSCTL_B200_MINB_BIG=$M -DSCTL_B200_EVAL_THREADS=$T -DSCTL_B200_UNROLL=$U -DSCTL_B200_EVAL_TILE=${TL:-128} -DSCTL_B200_EVAL_STAGES=${ST:-4} ;;
     *) echo "unknown variant $v"; exit 1 ;;
   esac
 done

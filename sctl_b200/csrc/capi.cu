@@ -172,12 +172,12 @@ static EvalPlan make_plan(const EvalEntry& E, int dtype, int64_t Nt, int64_t Ns,
   P.n_ttiles = (Nt + (long long)EVAL_THREADS * R - 1) / ((long long)EVAL_THREADS * R);
   P.nt_stride = (Nt + 31) / 32 * 32;
   // split the source range until there are ~64 CTAs per resident slot (tail <= ~1.5 %), keeping at least
-  // 16 tiles (2048 sources) per chunk and at most 1 GiB of partial sums
+  // 2 tiles (512 sources) per chunk and at most 1 GiB of partial sums
   const int occ = E.occupancy[P.rvar][P.newton]();
   const long long slots = (long long)occ * sms;
   const long long want = (long long)env_int("SCTL_B200_CTAS_PER_SLOT", 64) * slots;
   long long chunks = (want + P.n_ttiles - 1) / P.n_ttiles;
-  const long long max_by_tiles = P.n_tiles / 16 > 0 ? P.n_tiles / 16 : 1;
+  const long long max_by_tiles = P.n_tiles / 2 > 0 ? P.n_tiles / 2 : 1;
   const long long max_by_mem = (long long)((1ull << 30) / ((size_t)E.k1 * 8 * (size_t)P.nt_stride));
   if (chunks > max_by_tiles) chunks = max_by_tiles;
   if (chunks > max_by_mem) chunks = max_by_mem;

@@ -77,6 +77,35 @@ __device__ __forceinline__ double rsqrt_masked(double r2) {
   return fma(y0, q, y0);
 }
 
+// ---------------------------------------------------------------------------------------------
+// UNMASKED variants for the fast path of eval_kernel: no r2 == 0 test at all (r2 == 0 or denormal gives
+// inf/NaN, which the kernel detects once per source tile and repairs by re-running that tile with
+// rsqrt_masked). On the FP64 pipe every co-issued integer instruction costs ~1.2 issue cycles
+// (profiles/r01b_fp64_micro.txt), so dropping ISETP + SEL + the zeroing of the seed's low word is worth ~7 %.
+// The seed's LOW word is left undefined: MUFU.RSQ64H only defines the high word and the cubic step below
+// tolerates a 2^-20 relative perturbation of the seed (remainder 5/16 e^3 with |e| < 2^-18: < 2e-17).
+// ---------------------------------------------------------------------------------------------
+// `lo_any` supplies the (irrelevant) low word of the seed: pass a value whose 64-bit register dies at this point
+// (the partial sum dx^2 + dy^2), so that the seed can be built in that register pair without a move.
+__device__ __forceinline__ double rsqrt_unmasked_full(double r2, double lo_any) {
+  double seed;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(seed) : "d"(r2));
+  const double y0 = __hiloint2double(__double2hiint(seed), __double2loint(lo_any));
+  const double t = r2 * y0;
+  const double e = fma(-t, y0, 1.0);
+  const double p = fma(e, 0.375, 0.5);
+  const double q = e * p;
+  return fma(y0, q, y0);
+}
+__device__ __forceinline__ float rsqrt_unmasked_full(float r2, float) {
+  float y0;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y0) : "f"(r2));
+  const float t = r2 * y0;
+  const float e = fmaf(-t, y0, 1.0f);
+  const float h = 0.5f * y0;
+  return fmaf(h, e, y0);
+}
+
 // FP32: MUFU.RSQ (rsqrt.approx.ftz.f32, ~2^-22.4) + one Newton step for full precision, as the
 // reference's 1 iteration at digits = 6 (intrin-wrapper.hpp:3026).
 template <int NEWTON>

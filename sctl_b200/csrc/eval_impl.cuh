@@ -16,8 +16,12 @@
 //     and a second tiny kernel adds them in a FIXED order -> results are run-to-run deterministic.
 //   * the scale factor is applied once after the sum and v_trg is accumulated into
 //     (generic-kernel.txx:182-186) by whichever kernel finishes the sum.
-//   * FP32: per-tile f32 accumulators are flushed into f64 accumulators after every tile so that
-//     16M-source sums stay inside 1e-5 (the reference accumulates in plain f32).
+//   * every tile is summed into per-tile accumulators that are flushed into f64 running sums after the tile
+//     (FP32: 16M-source sums stay inside 1e-5, the reference accumulates in plain f32; FP64: blocked
+//     summation, slightly more accurate than the reference's single in-order accumulator).
+//   * the full-precision instantiations carry NO r2 == 0 test in the hot loop: a coincident pair turns the
+//     tile's partial sums non-finite, which is detected once per tile and repaired by re-running that tile
+//     with the masked rsqrt (exactly-zero contribution, kernel_functions.hpp:28).
 #pragma once
 #include "ukernels.cuh"
 
@@ -28,15 +32,15 @@ namespace sctl_b200 {
 #define SCTL_B200_EVAL_THREADS 128
 #endif
 #ifndef SCTL_B200_EVAL_TILE
-#define SCTL_B200_EVAL_TILE 128
+#define SCTL_B200_EVAL_TILE 256
 #endif
 #ifndef SCTL_B200_EVAL_STAGES
-#define SCTL_B200_EVAL_STAGES 4
+#define SCTL_B200_EVAL_STAGES 3
 #endif
 #ifndef SCTL_B200_UNROLL
-#define SCTL_B200_UNROLL 2
+#define SCTL_B200_UNROLL 1
 #endif
-constexpr int EVAL_THREADS = SCTL_B200_EVAL_THREADS;  // 4 warps; 4 CTAs/SM at <=128 registers
+constexpr int EVAL_THREADS = SCTL_B200_EVAL_THREADS;  // 4 warps; 2 CTAs/SM at R = 6 (212 registers): ILP, not occupancy, hides the FP64 latency
 constexpr int EVAL_TILE = SCTL_B200_EVAL_TILE;        // sources per shared-memory stage
 constexpr int EVAL_STAGES = SCTL_B200_EVAL_STAGES;    // ring depth (tile k-1's slot is refilled while tile k is consumed)
 constexpr int EVAL_UNROLL = SCTL_B200_UNROLL;         // source-loop unroll factor
@@ -88,10 +92,6 @@ __global__ void __launch_bounds__(256) pack_kernel(const Real* __restrict__ r_sr
 // ---------------------------------------------------------------------------------------------
 // eval: the O(Ns*Nt) kernel
 // ---------------------------------------------------------------------------------------------
-template <class Real> struct AccFlush;  // FP32 tiles are flushed into f64 accumulators
-template <> struct AccFlush<double> { static constexpr bool value = false; };
-template <> struct AccFlush<float> { static constexpr bool value = true; };
-
 template <class Ker, class Real, int R, int NEWTON, int MINB>
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalParams p) {
   constexpr int REC = rec_len<Ker, Real>();
@@ -134,8 +134,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
   const long long t_base = (long long)blockIdx.x * (EVAL_THREADS * R) + tid;
   const Real* r_trg = reinterpret_cast<const Real*>(p.r_trg);
   Real xt[R], yt[R], zt[R];
-  Real acc[R][NACC];
-  double acc64[AccFlush<Real>::value ? R : 1][NACC];
+  Real tacc[R][NACC];    // partial sums of the current source tile
+  double acc[R][NACC];   // running sums over tiles, always f64 (see FP32 note in the header comment)
 #pragma unroll
   for (int r = 0; r < R; r++) {
     long long t = t_base + (long long)r * EVAL_THREADS;
@@ -144,17 +144,24 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
     yt[r] = r_trg[t * 3 + 1];
     zt[r] = r_trg[t * 3 + 2];
 #pragma unroll
-    for (int k = 0; k < NACC; k++) {
-      acc[r][k] = (Real)0;
-      if (AccFlush<Real>::value) acc64[r][k] = 0.0;
-    }
+    for (int k = 0; k < NACC; k++) acc[r][k] = 0.0;
   }
+
+  // Full-precision instantiations run the tile UNMASKED (no r2 == 0 test in the hot loop) and repair the
+  // rare tile that held a coincident pair; the relaxed-digits instantiations keep the masked seed.
+  constexpr bool FAST = (NEWTON == (sizeof(Real) == 8 ? 2 : 1));
 
   for (int k = 0; k < ntile; k++) {
     const int stage = k % EVAL_STAGES;
     const uint32_t parity = (uint32_t)(k / EVAL_STAGES) & 1u;
     mbar_wait(&full_bar[stage], parity);
     const V* tile = reinterpret_cast<const V*>(tiles + (size_t)stage * EVAL_TILE * REC);
+
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+#pragma unroll
+      for (int q = 0; q < NACC; q++) tacc[r][q] = (Real)0;
+    }
 
 #pragma unroll EVAL_UNROLL
     for (int s = 0; s < EVAL_TILE; s++) {
@@ -166,23 +173,56 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
         const Real dx = xt[r] - src[0];
         const Real dy = yt[r] - src[1];
         const Real dz = zt[r] - src[2];
-        Real r2 = dx * dx;
-        r2 = fma(dy, dy, r2);
-        r2 = fma(dz, dz, r2);
-        const Real rinv = rsqrt_masked<NEWTON>(r2);
-        Ker::apply(acc[r], dx, dy, dz, rinv, src + 3);
+        Real r2p = dx * dx;
+        r2p = fma(dy, dy, r2p);
+        const Real r2 = fma(dz, dz, r2p);
+        const Real rinv = FAST ? rsqrt_unmasked_full(r2, r2p) : rsqrt_masked<NEWTON>(r2);
+        Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
       }
     }
 
-    if (AccFlush<Real>::value) {
+    if (FAST) {
+      // A pair with r2 == 0 (or denormal) made rinv inf/NaN and poisoned this tile's partial sums: detect it
+      // with one add chain per target and redo the tile for that thread with the masked rsqrt. Tiles holding
+      // coincident points are rare (one per target when targets == sources), so the slow loop is not unrolled.
+      bool bad = false;
 #pragma unroll
       for (int r = 0; r < R; r++) {
+        Real sum = tacc[r][0];
 #pragma unroll
-        for (int q = 0; q < NACC; q++) {
-          acc64[r][q] += (double)acc[r][q];
-          acc[r][q] = (Real)0;
+        for (int q = 1; q < NACC; q++) sum += tacc[r][q];
+        bad |= !(fabs(sum) <= (Real)(sizeof(Real) == 8 ? 1.7976931348623157e308 : 3.402823466e38));
+      }
+      if (bad) {
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+#pragma unroll
+          for (int q = 0; q < NACC; q++) tacc[r][q] = (Real)0;
+        }
+#pragma unroll 1
+        for (int s = 0; s < EVAL_TILE; s++) {
+          Real src[REC];
+#pragma unroll
+          for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];
+#pragma unroll
+          for (int r = 0; r < R; r++) {
+            const Real dx = xt[r] - src[0];
+            const Real dy = yt[r] - src[1];
+            const Real dz = zt[r] - src[2];
+            Real r2 = dx * dx;
+            r2 = fma(dy, dy, r2);
+            r2 = fma(dz, dz, r2);
+            const Real rinv = rsqrt_masked<NEWTON>(r2);
+            Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
+          }
         }
       }
+    }
+
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+#pragma unroll
+      for (int q = 0; q < NACC; q++) acc[r][q] += (double)tacc[r][q];
     }
 
     // Release the stage. Warp 0 then refills the slot that tile k-1 used (released by every warp about one
@@ -210,7 +250,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
     if (t >= p.Nt) continue;
     double a[NACC], out[K1];
 #pragma unroll
-    for (int q = 0; q < NACC; q++) a[q] = AccFlush<Real>::value ? acc64[r][q] : (double)acc[r][q];
+    for (int q = 0; q < NACC; q++) a[q] = acc[r][q];
     Ker::finalize(out, a);
     if (p.n_chunks == 1) {
       Real* v = reinterpret_cast<Real*>(p.v_trg) + t * K1;

@@ -8,15 +8,15 @@ namespace {
 
 using Real = SCTL_B200_REAL;
 #ifndef SCTL_B200_RBIG
-#define SCTL_B200_RBIG 4
+#define SCTL_B200_RBIG 6
 #endif
 #ifndef SCTL_B200_MINB_BIG
-#define SCTL_B200_MINB_BIG 4
+#define SCTL_B200_MINB_BIG 2
 #endif
 #ifndef SCTL_B200_ONLY_KERNEL
 #define SCTL_B200_ONLY_KERNEL -1  // >= 0: instantiate only that kernel id (fast variant builds for tuning sweeps)
 #endif
-constexpr int RBIG = SCTL_B200_RBIG;  // throughput variant
+constexpr int RBIG = SCTL_B200_RBIG;  // throughput variant (profiles/r01d_variant_sweep.txt: R 6, unroll 1, 256-source tiles)
 constexpr int RSMALL = 1;             // small-Nt variant
 constexpr bool IS_F32 = sizeof(Real) == 4;
 
@@ -28,7 +28,10 @@ cudaError_t pack_t(const void* r_src, const void* n_src, const void* v_src, void
   return cudaGetLastError();
 }
 
-template <int R> constexpr int minb_for() { return R == RBIG ? SCTL_B200_MINB_BIG : 8; }
+template <int R> constexpr int minb_for() { return R > 1 ? SCTL_B200_MINB_BIG : 8; }
+// targets per thread of the throughput variant: kernels with more than 4 accumulators per target (Stokes FxT: 6)
+// take 4 so that coordinates + per-tile + running accumulators stay in registers
+template <class Ker> constexpr int rbig_for() { return (Ker::NACC > 4 && RBIG > 4) ? 4 : RBIG; }
 
 template <class Ker, int R, int NEWTON>
 cudaError_t eval_t(const EvalParams& p, long long n_ttiles, cudaStream_t st) {
@@ -90,22 +93,22 @@ EvalEntry make_entry() {
   e.k1 = Ker::K1;
   e.nd = Ker::ND;
   e.R[0] = RSMALL;
-  e.R[1] = RBIG;
+  e.R[1] = rbig_for<Ker>();
   e.pack = pack_t<Ker>;
   e.reduce = reduce_t<Ker>;
   // f32 has refinement levels 0 and 1 only; level 2 aliases level 1
   e.eval[0][0] = eval_t<Ker, RSMALL, 0>;
   e.eval[0][1] = eval_t<Ker, RSMALL, 1>;
   e.eval[0][2] = eval_t<Ker, RSMALL, IS_F32 ? 1 : 2>;
-  e.eval[1][0] = eval_t<Ker, RBIG, 0>;
-  e.eval[1][1] = eval_t<Ker, RBIG, 1>;
-  e.eval[1][2] = eval_t<Ker, RBIG, IS_F32 ? 1 : 2>;
+  e.eval[1][0] = eval_t<Ker, rbig_for<Ker>(), 0>;
+  e.eval[1][1] = eval_t<Ker, rbig_for<Ker>(), 1>;
+  e.eval[1][2] = eval_t<Ker, rbig_for<Ker>(), IS_F32 ? 1 : 2>;
   e.occupancy[0][0] = occ_t<Ker, RSMALL, 0>;
   e.occupancy[0][1] = occ_t<Ker, RSMALL, 1>;
   e.occupancy[0][2] = occ_t<Ker, RSMALL, IS_F32 ? 1 : 2>;
-  e.occupancy[1][0] = occ_t<Ker, RBIG, 0>;
-  e.occupancy[1][1] = occ_t<Ker, RBIG, 1>;
-  e.occupancy[1][2] = occ_t<Ker, RBIG, IS_F32 ? 1 : 2>;
+  e.occupancy[1][0] = occ_t<Ker, rbig_for<Ker>(), 0>;
+  e.occupancy[1][1] = occ_t<Ker, rbig_for<Ker>(), 1>;
+  e.occupancy[1][2] = occ_t<Ker, rbig_for<Ker>(), IS_F32 ? 1 : 2>;
   e.kmat[0] = kmat_t<Ker, 0>;
   e.kmat[1] = kmat_t<Ker, 1>;
   e.kmat[2] = kmat_t<Ker, IS_F32 ? 1 : 2>;

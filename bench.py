@@ -294,7 +294,7 @@ def run_b200_arm(args):
     pairs_per_launch = float(n) * float(t1 - t0)
     ach = pairs_per_launch * FLOPS_REF / (kern_ms * 1e-3) * 1e-12
     roofline = {"bound": "fp64_cuda_core", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf if peak_tf else None,
-                "traffic": None, "kernel": "eval_kernel<KStokesFxU,double,R=4,NEWTON=2>", "kernel_ms": kern_ms,
+                "traffic": None, "kernel": "eval_kernel<KStokesFxU,double,R=6,NEWTON=2>", "kernel_ms": kern_ms,
                 "peak_source": "measured live: register-resident DFMA chain (sctl_b200_measure_peak), 2 flop per FMA; MEASURED_PEAKS.json has no FP64 figure",
                 "flops_per_pair_algorithmic": FLOPS_REF, "fp64_instr_per_pair_executed": FP64_INSTR_PER_PAIR,
                 "fp64_pipe_frac": pairs_per_launch * FP64_INSTR_PER_PAIR * 2 / (kern_ms * 1e-3) * 1e-12 / peak_tf if peak_tf else None}

@@ -110,6 +110,28 @@ SCTL_B200_API int sctl_b200_buf_upload(void* d_ptr, const void* host, int dtype,
 SCTL_B200_API int sctl_b200_buf_download(const void* d_ptr, void* host, int dtype, int64_t n);
 SCTL_B200_API int sctl_b200_buf_destroy(void* d_ptr);
 
+/* Device-resident particle context — the GPU-aware counterpart of ParticleFMM's registry and EvalDirect
+ * (fmm-wrapper.txx:297-479 and :490-562). Coordinates, normals, densities and the packed source records stay in
+ * HBM between calls; records are re-packed only when a source's coordinates or density changed. Sources / targets
+ * are declared with the dims the reference derives from the kernels passed to AddSrc / AddTrg
+ * (fmm-wrapper.txx:306-309, :346). Inputs are COPIED at Set* time like the reference does (:447-448), from host
+ * pointers or (SCTL_B200_DEVICE_PTRS) device pointers. eval_direct OVERWRITES U (:501-502) with the sum over every
+ * source that has an S2T kernel for the target, in (src, trg) name order like the reference's std::map walk (:514).
+ * Far-field FMM (PVFMM) is not part of this library: Eval == EvalDirect, as in a reference build without PVFMM (:481-489). */
+SCTL_B200_API int sctl_b200_fmm_create(void** fmm, int dtype);
+SCTL_B200_API int sctl_b200_fmm_destroy(void* fmm);
+SCTL_B200_API int sctl_b200_fmm_set_accuracy(void* fmm, int digits);                                   /* SetAccuracy */
+SCTL_B200_API int sctl_b200_fmm_add_src(void* fmm, const char* name, int src_dim, int normal_dim);     /* AddSrc  fmm-wrapper.txx:297 */
+SCTL_B200_API int sctl_b200_fmm_add_trg(void* fmm, const char* name, int trg_dim);                     /* AddTrg  :337 */
+SCTL_B200_API int sctl_b200_fmm_set_kernel_s2t(void* fmm, const char* src_name, const char* trg_name, int kernel_id); /* SetKernelS2T :371 */
+SCTL_B200_API int sctl_b200_fmm_delete_src(void* fmm, const char* name);                               /* DeleteSrc :407 */
+SCTL_B200_API int sctl_b200_fmm_delete_trg(void* fmm, const char* name);                               /* DeleteTrg :419 */
+SCTL_B200_API int sctl_b200_fmm_set_src_coord(void* fmm, const char* name, int64_t Ns, const void* r_src, const void* n_src, unsigned flags); /* :444 */
+SCTL_B200_API int sctl_b200_fmm_set_src_density(void* fmm, const char* name, int64_t n, const void* v_src, unsigned flags);                  /* :462 */
+SCTL_B200_API int sctl_b200_fmm_set_trg_coord(void* fmm, const char* name, int64_t Nt, const void* r_trg, unsigned flags);                   /* :467 */
+SCTL_B200_API int sctl_b200_fmm_trg_count(void* fmm, const char* name, int64_t* Nt, int* trg_dim);
+SCTL_B200_API int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t n, unsigned flags);                            /* :490 */
+
 /* Device management. One process per GPU is the normal multi-GPU mode (each MPI / torchrun rank calls
  * sctl_b200_set_device(local_rank) once, as the reference's ranks each own a target block,
  * fmm-wrapper.txx:504-510). */

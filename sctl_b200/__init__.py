@@ -6,6 +6,7 @@ sctl_b200/lib/libsctl_b200.so (hand-written sm_100a CUDA behind the C ABI of inc
 package is the Python mirror of the reference's C++ interface used by tests, bench.py and torchrun drivers.
 """
 from . import capi  # noqa: F401
+from .fmm import ParticleFMM  # noqa: F401
 from .kernels import (  # noqa: F401
     KERNEL_BY_NAME,
     KERNELS,
@@ -20,5 +21,5 @@ from .kernels import (  # noqa: F401
     Stokes3D_FxUP,
 )
 
-__all__ = ["capi", "GenericKernel", "KERNELS", "KERNEL_BY_NAME", "Laplace3D_FxU", "Laplace3D_DxU", "Laplace3D_FxdU", "Stokes3D_FxU",
+__all__ = ["capi", "ParticleFMM", "GenericKernel", "KERNELS", "KERNEL_BY_NAME", "Laplace3D_FxU", "Laplace3D_DxU", "Laplace3D_FxdU", "Stokes3D_FxU",
            "Stokes3D_DxU", "Stokes3D_FxT", "Stokes3D_FSxU", "Stokes3D_FxUP"]

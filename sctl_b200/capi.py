@@ -30,6 +30,19 @@ SYMBOLS = {
     "sctl_b200_buf_upload": (c_int, [c_void_p, c_void_p, c_int, c_int64]),
     "sctl_b200_buf_download": (c_int, [c_void_p, c_void_p, c_int, c_int64]),
     "sctl_b200_buf_destroy": (c_int, [c_void_p]),
+    "sctl_b200_fmm_create": (c_int, [POINTER(c_void_p), c_int]),
+    "sctl_b200_fmm_destroy": (c_int, [c_void_p]),
+    "sctl_b200_fmm_set_accuracy": (c_int, [c_void_p, c_int]),
+    "sctl_b200_fmm_add_src": (c_int, [c_void_p, c_char_p, c_int, c_int]),
+    "sctl_b200_fmm_add_trg": (c_int, [c_void_p, c_char_p, c_int]),
+    "sctl_b200_fmm_set_kernel_s2t": (c_int, [c_void_p, c_char_p, c_char_p, c_int]),
+    "sctl_b200_fmm_delete_src": (c_int, [c_void_p, c_char_p]),
+    "sctl_b200_fmm_delete_trg": (c_int, [c_void_p, c_char_p]),
+    "sctl_b200_fmm_set_src_coord": (c_int, [c_void_p, c_char_p, c_int64, c_void_p, c_void_p, c_uint]),
+    "sctl_b200_fmm_set_src_density": (c_int, [c_void_p, c_char_p, c_int64, c_void_p, c_uint]),
+    "sctl_b200_fmm_set_trg_coord": (c_int, [c_void_p, c_char_p, c_int64, c_void_p, c_uint]),
+    "sctl_b200_fmm_trg_count": (c_int, [c_void_p, c_char_p, POINTER(c_int64), POINTER(c_int)]),
+    "sctl_b200_fmm_eval_direct": (c_int, [c_void_p, c_char_p, c_void_p, c_int64, c_uint]),
     "sctl_b200_device_count": (c_int, [POINTER(c_int)]),
     "sctl_b200_set_device": (c_int, [c_int]),
     "sctl_b200_get_device": (c_int, [POINTER(c_int)]),

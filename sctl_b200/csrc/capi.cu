@@ -190,8 +190,46 @@ static EvalPlan make_plan(const EvalEntry& E, int dtype, int64_t Nt, int64_t Ns,
   return P;
 }
 
-// All pointers are device pointers on the current device. Enqueues on `st`, does not synchronise.
-// ev (optional): 4 events recorded around pack | eval | reduce.
+// pack: AoS (r_src, n_src, v_src) -> tile-padded source records in `rec` (device). Ns_pad records are written.
+static int64_t padded_sources(int64_t Ns) { return (Ns + EVAL_TILE - 1) / EVAL_TILE * EVAL_TILE; }
+static int pack_device(int kernel_id, int dtype, int64_t Ns, const void* r_src, const void* n_src, const void* v_src, void* rec, cudaStream_t st) {
+  const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
+  if (Ns == 0) return 0;
+  CU_TRY(E.pack(r_src, n_src, v_src, rec, Ns, padded_sources(Ns), st));
+  return 0;
+}
+
+// The O(Ns*Nt) part on pre-packed records. All pointers are device pointers on the current device.
+// Enqueues on `st`, does not synchronise.
+static int eval_packed_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* rec, void* v_trg, int digits,
+                              bool accumulate, cudaStream_t st, int sms, cudaEvent_t* ev) {
+  const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
+  const EvalPlan P = make_plan(E, dtype, Nt, Ns, digits, sms);
+  DevAlloc partial;
+  if (P.n_chunks > 1) {
+    int rc = partial.alloc((size_t)P.n_chunks * E.k1 * (size_t)P.nt_stride * sizeof(double), st);
+    if (rc) return rc;
+  }
+  EvalParams p{};
+  p.r_trg = r_trg;
+  p.rec = rec;
+  p.v_trg = v_trg;
+  p.partial = (double*)partial.p;
+  p.Nt = Nt;
+  p.nt_stride = P.nt_stride;
+  p.n_tiles = (int)P.n_tiles;
+  p.tiles_per_chunk = P.tiles_per_chunk;
+  p.n_chunks = P.n_chunks;
+  p.accumulate = accumulate ? 1 : 0;
+  p.scale = kernel_scale(kernel_id);
+  CU_TRY(E.eval[P.rvar][P.newton](p, P.n_ttiles, st));
+  if (ev) CU_TRY(cudaEventRecord(ev[0], st));
+  if (P.n_chunks > 1) CU_TRY(E.reduce((const double*)partial.p, v_trg, Nt, P.nt_stride, P.n_chunks, p.scale, p.accumulate, st));
+  if (ev) CU_TRY(cudaEventRecord(ev[1], st));
+  return 0;
+}
+
+// pack + eval (+ reduce). ev (optional): 4 events recorded around pack | eval | reduce.
 static int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
                        const void* v_src, void* v_trg, int digits, bool accumulate, cudaStream_t st, int sms, cudaEvent_t* ev) {
   const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
@@ -204,36 +242,13 @@ static int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const v
     return 0;
   }
   if (Ns > (int64_t)EVAL_TILE * 0x7fffffffLL) return set_error(SCTL_B200_ERR_ARG, "Ns too large");
-  const EvalPlan P = make_plan(E, dtype, Nt, Ns, digits, sms);
-
-  DevAlloc rec, partial;
-  int rc = rec.alloc((size_t)P.Ns_pad * E.rec_len * esz, st);
+  DevAlloc rec;
+  int rc = rec.alloc((size_t)padded_sources(Ns) * E.rec_len * esz, st);
   if (rc) return rc;
-  if (P.n_chunks > 1) {
-    rc = partial.alloc((size_t)P.n_chunks * E.k1 * (size_t)P.nt_stride * sizeof(double), st);
-    if (rc) return rc;
-  }
   if (ev) CU_TRY(cudaEventRecord(ev[0], st));
-  CU_TRY(E.pack(r_src, n_src, v_src, rec.p, Ns, P.Ns_pad, st));
+  if ((rc = pack_device(kernel_id, dtype, Ns, r_src, n_src, v_src, rec.p, st))) return rc;
   if (ev) CU_TRY(cudaEventRecord(ev[1], st));
-
-  EvalParams p{};
-  p.r_trg = r_trg;
-  p.rec = rec.p;
-  p.v_trg = v_trg;
-  p.partial = (double*)partial.p;
-  p.Nt = Nt;
-  p.nt_stride = P.nt_stride;
-  p.n_tiles = (int)P.n_tiles;
-  p.tiles_per_chunk = P.tiles_per_chunk;
-  p.n_chunks = P.n_chunks;
-  p.accumulate = accumulate ? 1 : 0;
-  p.scale = kernel_scale(kernel_id);
-  CU_TRY(E.eval[P.rvar][P.newton](p, P.n_ttiles, st));
-  if (ev) CU_TRY(cudaEventRecord(ev[2], st));
-  if (P.n_chunks > 1) CU_TRY(E.reduce((const double*)partial.p, v_trg, Nt, P.nt_stride, P.n_chunks, p.scale, p.accumulate, st));
-  if (ev) CU_TRY(cudaEventRecord(ev[3], st));
-  return 0;
+  return eval_packed_device(kernel_id, dtype, Nt, Ns, r_trg, rec.p, v_trg, digits, accumulate, st, sms, ev ? ev + 2 : nullptr);
 }
 
 static int kmat_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src, void* M,
@@ -380,9 +395,316 @@ static int kmat_host(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const voi
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Device-resident particle context: the GPU-aware counterpart of ParticleFMM's registry + EvalDirect
+// (reference: fmm-wrapper.txx:297-479 registry, :490-562 EvalDirect). Coordinates, normals, densities and
+// the packed source records stay in HBM between calls; records are re-packed only when the coordinates or
+// the density of that source changed (coordinates are set once, the density changes every solver
+// iteration: boundary_integral.txx:777-778 vs :1054).
+// ------------------------------------------------------------------------------------------------
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  ~DevBuf() {
+    if (p) cudaFree(p);
+  }
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+      return set_error(SCTL_B200_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", bytes, cudaGetErrorString(e));
+    }
+    cap = bytes;
+    return 0;
+  }
+};
+struct FmmSrc {
+  int src_dim = 0, normal_dim = 0;
+  int64_t Ns = 0;    // from the coordinates
+  int64_t n_den = 0; // elements of the density last set
+  DevBuf X, Xn, F;
+  unsigned long long version = 0;  // bumped by SetSrcCoord / SetSrcDensity
+};
+struct FmmTrg {
+  int trg_dim = 0;
+  int64_t Nt = 0;
+  DevBuf X, U;
+};
+struct FmmS2T {
+  int kernel_id = -1;
+  DevBuf rec;
+  unsigned long long packed_version = ~0ull;
+};
+struct FmmCtx {
+  int dtype = SCTL_B200_F64;
+  int dev = 0;
+  int digits = -1;  // ParticleFMM default digits_ = 10 is an FMM tolerance; the direct sum is evaluated at SetAccuracy's value
+  std::mutex mu;
+  std::vector<std::pair<std::string, FmmSrc*>> src;
+  std::vector<std::pair<std::string, FmmTrg*>> trg;
+  std::vector<std::pair<std::pair<std::string, std::string>, FmmS2T*>> s2t;  // kept sorted like std::map (src, trg)
+  ~FmmCtx() {
+    for (auto& a : src) delete a.second;
+    for (auto& a : trg) delete a.second;
+    for (auto& a : s2t) delete a.second;
+  }
+  FmmSrc* find_src(const char* n) {
+    for (auto& a : src)
+      if (a.first == n) return a.second;
+    return nullptr;
+  }
+  FmmTrg* find_trg(const char* n) {
+    for (auto& a : trg)
+      if (a.first == n) return a.second;
+    return nullptr;
+  }
+};
+
+static int fmm_upload(DevBuf& b, const void* src, size_t bytes, bool device_ptrs, cudaStream_t st) {
+  int rc = b.reserve(bytes ? bytes : 16);
+  if (rc) return rc;
+  if (bytes) CU_TRY(cudaMemcpyAsync(b.p, src, bytes, device_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+  return 0;
+}
+
 }  // namespace sctl_b200
 
 using namespace sctl_b200;
+
+#define FMM_ENTER(h)                                                                       \
+  if (!(h)) return set_error(SCTL_B200_ERR_ARG, "null context");                           \
+  FmmCtx* C = (FmmCtx*)(h);                                                                \
+  std::lock_guard<std::mutex> lk__(C->mu);                                                 \
+  CU_TRY(cudaSetDevice(C->dev));                                                           \
+  DevCtx* c = nullptr;                                                                     \
+  {                                                                                        \
+    int rc__ = get_ctx(&c);                                                                \
+    if (rc__) return rc__;                                                                 \
+  }
+
+extern "C" {
+
+int sctl_b200_fmm_create(void** fmm, int dtype) {
+  if (!fmm) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return set_error(SCTL_B200_ERR_DTYPE, "unknown dtype %d", dtype);
+  DevCtx* c = nullptr;
+  int rc = get_ctx(&c);
+  if (rc) return rc;
+  FmmCtx* C = new FmmCtx();
+  C->dtype = dtype;
+  C->dev = c->dev;
+  *fmm = C;
+  return 0;
+}
+int sctl_b200_fmm_destroy(void* fmm) {
+  if (!fmm) return 0;
+  FmmCtx* C = (FmmCtx*)fmm;
+  cudaSetDevice(C->dev);
+  cudaDeviceSynchronize();
+  delete C;
+  return 0;
+}
+int sctl_b200_fmm_set_accuracy(void* fmm, int digits) {
+  if (!fmm) return set_error(SCTL_B200_ERR_ARG, "null context");
+  FmmCtx* C = (FmmCtx*)fmm;
+  std::lock_guard<std::mutex> lk(C->mu);
+  C->digits = digits;
+  return 0;
+}
+int sctl_b200_fmm_add_src(void* fmm, const char* name, int src_dim, int normal_dim) {
+  if (!fmm || !name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  FmmCtx* C = (FmmCtx*)fmm;
+  std::lock_guard<std::mutex> lk(C->mu);
+  if (C->find_src(name)) return set_error(SCTL_B200_ERR_ARG, "Source name already exists.");
+  if (src_dim < 1 || src_dim > 4 || (normal_dim != 0 && normal_dim != 3)) return set_error(SCTL_B200_ERR_ARG, "bad source dims");
+  FmmSrc* s = new FmmSrc();
+  s->src_dim = src_dim;
+  s->normal_dim = normal_dim;
+  C->src.emplace_back(name, s);
+  return 0;
+}
+int sctl_b200_fmm_add_trg(void* fmm, const char* name, int trg_dim) {
+  if (!fmm || !name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  FmmCtx* C = (FmmCtx*)fmm;
+  std::lock_guard<std::mutex> lk(C->mu);
+  if (C->find_trg(name)) return set_error(SCTL_B200_ERR_ARG, "Target name already exists.");
+  if (trg_dim < 1 || trg_dim > 9) return set_error(SCTL_B200_ERR_ARG, "bad target dim");
+  FmmTrg* t = new FmmTrg();
+  t->trg_dim = trg_dim;
+  C->trg.emplace_back(name, t);
+  return 0;
+}
+int sctl_b200_fmm_set_kernel_s2t(void* fmm, const char* src_name, const char* trg_name, int kernel_id) {
+  if (!fmm || !src_name || !trg_name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if (kernel_id < 0 || kernel_id >= NUM_KERNELS) return set_error(SCTL_B200_ERR_KERNEL, "unknown kernel id %d", kernel_id);
+  FmmCtx* C = (FmmCtx*)fmm;
+  std::lock_guard<std::mutex> lk(C->mu);
+  FmmSrc* s = C->find_src(src_name);
+  FmmTrg* t = C->find_trg(trg_name);
+  if (!s) return set_error(SCTL_B200_ERR_ARG, "Source name does not exists.");
+  if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exists.");
+  const KernelInfo& ki = KINFO[kernel_id];
+  // CheckKernelDims (fmm-wrapper.txx:567-605): the S2T kernel must agree with the dims the source / target were declared with
+  if (ki.src_dim != s->src_dim || ki.normal_dim != s->normal_dim || ki.trg_dim != t->trg_dim)
+    return set_error(SCTL_B200_ERR_ARG, "kernel %s (src %d, normal %d, trg %d) does not match source '%s' (%d, %d) / target '%s' (%d)", ki.name,
+                     ki.src_dim, ki.normal_dim, ki.trg_dim, src_name, s->src_dim, s->normal_dim, trg_name, t->trg_dim);
+  const std::pair<std::string, std::string> key(src_name, trg_name);
+  for (auto& a : C->s2t)
+    if (a.first == key) {  // replaces an existing S2T kernel (fmm-wrapper.txx:376)
+      a.second->kernel_id = kernel_id;
+      a.second->packed_version = ~0ull;
+      return 0;
+    }
+  FmmS2T* d = new FmmS2T();
+  d->kernel_id = kernel_id;
+  auto it = C->s2t.begin();
+  while (it != C->s2t.end() && it->first < key) ++it;  // std::map iteration order of the reference (:514)
+  C->s2t.insert(it, std::make_pair(key, d));
+  return 0;
+}
+int sctl_b200_fmm_delete_src(void* fmm, const char* name) {
+  if (!fmm || !name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  FmmCtx* C = (FmmCtx*)fmm;
+  std::lock_guard<std::mutex> lk(C->mu);
+  cudaSetDevice(C->dev);
+  cudaDeviceSynchronize();
+  bool found = false;
+  for (size_t i = 0; i < C->src.size(); i++)
+    if (C->src[i].first == name) {
+      delete C->src[i].second;
+      C->src.erase(C->src.begin() + i);
+      found = true;
+      break;
+    }
+  if (!found) return set_error(SCTL_B200_ERR_ARG, "Source name does not exist.");
+  for (size_t i = C->s2t.size(); i-- > 0;)
+    if (C->s2t[i].first.first == name) {
+      delete C->s2t[i].second;
+      C->s2t.erase(C->s2t.begin() + i);
+    }
+  return 0;
+}
+int sctl_b200_fmm_delete_trg(void* fmm, const char* name) {
+  if (!fmm || !name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  FmmCtx* C = (FmmCtx*)fmm;
+  std::lock_guard<std::mutex> lk(C->mu);
+  cudaSetDevice(C->dev);
+  cudaDeviceSynchronize();
+  bool found = false;
+  for (size_t i = 0; i < C->trg.size(); i++)
+    if (C->trg[i].first == name) {
+      delete C->trg[i].second;
+      C->trg.erase(C->trg.begin() + i);
+      found = true;
+      break;
+    }
+  if (!found) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
+  for (size_t i = C->s2t.size(); i-- > 0;)
+    if (C->s2t[i].first.second == name) {
+      delete C->s2t[i].second;
+      C->s2t.erase(C->s2t.begin() + i);
+    }
+  return 0;
+}
+
+int sctl_b200_fmm_set_src_coord(void* fmm, const char* name, int64_t Ns, const void* r_src, const void* n_src, unsigned flags) {
+  FMM_ENTER(fmm);
+  FmmSrc* s = name ? C->find_src(name) : nullptr;
+  if (!s) return set_error(SCTL_B200_ERR_ARG, "Source name does not exist.");
+  if (Ns < 0 || (Ns > 0 && (!r_src || (s->normal_dim && !n_src)))) return set_error(SCTL_B200_ERR_ARG, "bad source coordinates");
+  const size_t esz = elem_size(C->dtype);
+  const bool dp = flags & SCTL_B200_DEVICE_PTRS;
+  int rc;
+  if ((rc = fmm_upload(s->X, r_src, (size_t)Ns * 3 * esz, dp, c->stream))) return rc;
+  if (s->normal_dim && (rc = fmm_upload(s->Xn, n_src, (size_t)Ns * s->normal_dim * esz, dp, c->stream))) return rc;
+  CU_TRY(cudaStreamSynchronize(c->stream));  // the caller may free its buffers after the call (the reference copies, fmm-wrapper.txx:447-448)
+  s->Ns = Ns;
+  s->version++;
+  return 0;
+}
+int sctl_b200_fmm_set_src_density(void* fmm, const char* name, int64_t n, const void* v_src, unsigned flags) {
+  FMM_ENTER(fmm);
+  FmmSrc* s = name ? C->find_src(name) : nullptr;
+  if (!s) return set_error(SCTL_B200_ERR_ARG, "Source name does not exist.");
+  if (n < 0 || (n > 0 && !v_src)) return set_error(SCTL_B200_ERR_ARG, "bad source density");
+  int rc = fmm_upload(s->F, v_src, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream);
+  if (rc) return rc;
+  CU_TRY(cudaStreamSynchronize(c->stream));
+  s->n_den = n;
+  s->version++;
+  return 0;
+}
+int sctl_b200_fmm_set_trg_coord(void* fmm, const char* name, int64_t Nt, const void* r_trg, unsigned flags) {
+  FMM_ENTER(fmm);
+  FmmTrg* t = name ? C->find_trg(name) : nullptr;
+  if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
+  if (Nt < 0 || (Nt > 0 && !r_trg)) return set_error(SCTL_B200_ERR_ARG, "bad target coordinates");
+  int rc = fmm_upload(t->X, r_trg, (size_t)Nt * 3 * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream);
+  if (rc) return rc;
+  CU_TRY(cudaStreamSynchronize(c->stream));
+  t->Nt = Nt;
+  return 0;
+}
+int sctl_b200_fmm_trg_count(void* fmm, const char* name, int64_t* Nt, int* trg_dim) {
+  if (!fmm || !name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  FmmCtx* C = (FmmCtx*)fmm;
+  std::lock_guard<std::mutex> lk(C->mu);
+  FmmTrg* t = C->find_trg(name);
+  if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
+  if (Nt) *Nt = t->Nt;
+  if (trg_dim) *trg_dim = t->trg_dim;
+  return 0;
+}
+
+// U[Nt*TrgDim] = sum over every source registered with an S2T kernel for this target (overwritten, fmm-wrapper.txx:501-502)
+int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t n, unsigned flags) {
+  FMM_ENTER(fmm);
+  FmmTrg* t = trg_name ? C->find_trg(trg_name) : nullptr;
+  if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
+  if (n != t->Nt * t->trg_dim) return set_error(SCTL_B200_ERR_ARG, "U must hold Nt*TrgDim = %lld values", (long long)(t->Nt * t->trg_dim));
+  if (n == 0) return 0;
+  if (!U) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  const size_t esz = elem_size(C->dtype);
+  const bool dp = flags & SCTL_B200_DEVICE_PTRS;
+  cudaStream_t st = c->stream;
+  void* dU = U;
+  int rc;
+  if (!dp) {
+    if ((rc = t->U.reserve((size_t)n * esz))) return rc;
+    dU = t->U.p;
+  }
+  bool first = true;
+  for (auto& a : C->s2t) {
+    if (a.first.second != trg_name) continue;
+    FmmSrc* s = C->find_src(a.first.first.c_str());
+    FmmS2T* d = a.second;
+    if (!s) return set_error(SCTL_B200_ERR_ARG, "Source name does not exist.");
+    if (s->n_den != s->Ns * s->src_dim)  // the reference asserts F.Dim() == Ns*SrcDim (fmm-wrapper.txx:533)
+      return set_error(SCTL_B200_ERR_ARG, "source '%s': density has %lld values, expected Ns*SrcDim = %lld", a.first.first.c_str(),
+                       (long long)s->n_den, (long long)(s->Ns * s->src_dim));
+    if (s->Ns == 0) continue;
+    const EvalEntry& E = (C->dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[d->kernel_id];
+    if (d->packed_version != s->version) {
+      if ((rc = d->rec.reserve((size_t)padded_sources(s->Ns) * E.rec_len * esz))) return rc;
+      if ((rc = pack_device(d->kernel_id, C->dtype, s->Ns, s->X.p, s->normal_dim ? s->Xn.p : nullptr, s->F.p, d->rec.p, st))) return rc;
+      d->packed_version = s->version;
+    }
+    if ((rc = eval_packed_device(d->kernel_id, C->dtype, t->Nt, s->Ns, t->X.p, d->rec.p, dU, C->digits, !first, st, c->sms, nullptr))) return rc;
+    first = false;
+  }
+  if (first) CU_TRY(cudaMemsetAsync(dU, 0, (size_t)n * esz, st));
+  if (!dp) CU_TRY(cudaMemcpyAsync(U, dU, (size_t)n * esz, cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  return 0;
+}
+
+}  // extern "C"
+
 
 extern "C" {
 

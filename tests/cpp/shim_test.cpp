@@ -14,6 +14,7 @@
 //         shim_test --no-gpu   checks that a compute call fails LOUDLY (abort through SCTL_ERROR) without a GPU
 #include <sctl.hpp>
 #include <sctl_b200/generic-kernel-b200.hpp>
+#include <sctl_b200/particle-fmm-b200.hpp>
 
 #include <cmath>
 #include <cstdio>
@@ -98,7 +99,7 @@ template <class UK, class Real> static void test_kernel(double tol) {
 }
 
 // the reference's own ParticleFMM test set-up (fmm-wrapper.txx:35-93) with two source types summed into one target
-template <class Real, template <class> class Wrap> static sctl::Vector<Real> run_particle_fmm(Long N) {
+template <class Real, template <class> class Wrap, template <class, Integer> class FMM = sctl::ParticleFMM> static sctl::Vector<Real> run_particle_fmm(Long N, int reps = 1) {
   using SL = sctl::GenericKernel<Wrap<sctl::kernel_impl::Stokes3D_FxU>>;
   using DL = sctl::GenericKernel<Wrap<sctl::kernel_impl::Stokes3D_DxU>>;
   using M2L = sctl::GenericKernel<Wrap<sctl::kernel_impl::Stokes3D_FSxU>>;
@@ -109,7 +110,7 @@ template <class Real, template <class> class Wrap> static sctl::Vector<Real> run
   sctl::Vector<Real> trg(N * 3), dl_coord(N * 3), dl_norml(N * 3), dl_den(N * 3), sl_coord((N + 7) * 3), sl_den((N + 7) * 3);
   fill(trg), fill(dl_coord), fill(dl_norml), fill(dl_den), fill(sl_coord), fill(sl_den);
   const sctl::Comm comm = sctl::Comm::Self();
-  sctl::ParticleFMM<Real, 3> fmm(comm);
+  FMM<Real, 3> fmm(comm);
   fmm.SetAccuracy(10);
   fmm.SetKernels(kernel_m2l, kernel_m2l, kernel_sl);
   fmm.AddTrg("Velocity", kernel_m2l, kernel_sl);
@@ -124,6 +125,12 @@ template <class Real, template <class> class Wrap> static sctl::Vector<Real> run
   fmm.SetSrcDensity("SingleLayer", sl_den);
   sctl::Vector<Real> U;
   fmm.EvalDirect(U, "Velocity");
+  for (int i = 1; i < reps; i++) {  // solver-loop pattern: only the density changes between evaluations (boundary_integral.txx:1054)
+    for (auto& a : dl_den) a = -a * (Real)0.5;
+    fmm.SetSrcDensity("DoubleLayer", dl_den);
+    U = 123;  // stale contents must be overwritten (fmm-wrapper.txx:501-502)
+    fmm.Eval(U, "Velocity");
+  }
   return U;
 }
 template <class K> struct Same : K {};  // never used: GPU path uses the kernel_impl types themselves
@@ -151,6 +158,14 @@ int main(int argc, char** argv) {
     const auto Ugf = run_particle_fmm<float, Identity>(3000);
     const auto Ucf = run_particle_fmm<float, CpuCopy>(3000);
     report("ParticleFMM<float,3>::EvalDirect (DL + SL -> Velocity)", rel_l2(Ugf, Ucf), 1e-5);
+  }
+  {  // the GPU-aware registry (device-resident coordinates + cached records) against the reference's ParticleFMM on the CPU
+    const auto Ug = run_particle_fmm<double, Identity, sctl_b200::ParticleFMM>(5000, 3);
+    const auto Uc = run_particle_fmm<double, CpuCopy>(5000, 3);
+    report("sctl_b200::ParticleFMM<double,3> registry, 3 density updates", rel_l2(Ug, Uc), 1e-12);
+    const auto Ugf = run_particle_fmm<float, Identity, sctl_b200::ParticleFMM>(3000, 2);
+    const auto Ucf = run_particle_fmm<float, CpuCopy>(3000, 2);
+    report("sctl_b200::ParticleFMM<float,3> registry, 2 density updates", rel_l2(Ugf, Ucf), 1e-5);
   }
   std::printf("launches issued by libsctl_b200: %lld\n", (long long)sctl_b200_launch_count());
   std::printf(g_fail ? "SHIM TEST FAILED (%d)\n" : "SHIM TEST PASSED\n", g_fail);

@@ -51,47 +51,99 @@ def parse_args():
 # clocks: sample nvidia-smi during the timed region (B200_PROFILING.md recipe)
 # ------------------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """Samples SM clock, power and throttle reasons of one GPU DURING the timed region, in-process through NVML (the
+    library nvidia-smi itself reads) from a background thread. A looping `nvidia-smi -lms 200` subprocess was measured to
+    slow the 2-GPU run by up to 50 % (profiles/r01g_*: 3.9 s vs 2.63 s per step), so it is only the fallback when pynvml
+    is missing."""
+    PERIOD_S = float(os.environ.get("SCTL_B200_SAMPLER_PERIOD", "0.5"))
+    MODE = os.environ.get("SCTL_B200_SAMPLER_MODE", "all")  # diagnostic: which NVML queries to issue
+
+    def __init__(self, gpu_index: int):
+        import threading
+
+        self.samples = []  # (sm_mhz, sm_max_mhz, power_w, reasons bitmask)
+        self._stop = threading.Event()
+        self._thread = None
+        self._proc = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[gpu_index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else gpu_index
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self._max = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+        except Exception:
+            self._nv = None
+            self._start_smi(gpu_index)
+
+    def _loop(self):
+        nv = self._nv
+        while not self._stop.is_set():
+            try:
+                m = self.MODE
+                self.samples.append((float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)) if m in ("all", "clock") else 0.0, float(self._max),
+                                     nv.nvmlDeviceGetPowerUsage(self._h) / 1000.0 if m in ("all", "power") else 0.0,
+                                     int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)) if m in ("all", "reasons") else 0))
+            except Exception:
+                pass
+            self._stop.wait(self.PERIOD_S)
+
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
-        self.p = None
+    def _start_smi(self, gpu_index):
+        self._f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
-                                      stdout=self.f, stderr=subprocess.DEVNULL)
+            self._proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "1000"],
+                                          stdout=self._f, stderr=subprocess.DEVNULL)
         except OSError:
-            self.p = None
+            self._proc = None
 
     def stop(self) -> dict:
-        out = {"sm_mhz": None, "sm_max_mhz": None, "power_w_max": None, "reasons": [], "samples": 0}
-        if self.p is None:
-            return out
-        self.p.terminate()
-        try:
-            self.p.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.p.kill()
-        self.f.flush()
-        self.f.seek(0)
-        sm, mx, pw, reasons = [], [], [], set()
+        out = {"sm_mhz": None, "sm_max_mhz": None, "power_w_max": None, "reasons": [], "samples": 0, "how": None}
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.f:
-            c = [x.strip() for x in line.split(",")]
-            if len(c) < 7:
-                continue
+        sm, mx, pw, reasons = [], [], [], set()
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join(timeout=5)
+            nv = self._nv
+            bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksEventReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": nv.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksEventReasonSwPowerCap}
+            for a, b, c, r in self.samples:
+                sm.append(a); mx.append(b); pw.append(c)
+                for nm in names:
+                    if r & bits[nm]:
+                        reasons.add(nm)
+            out["how"] = f"NVML in-process thread, every {self.PERIOD_S} s"
+        elif self._proc is not None:
+            self._proc.terminate()
             try:
-                sm.append(float(c[0])); mx.append(float(c[1])); pw.append(float(c[2]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, c[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        self.f.close()
-        try:
-            os.unlink(self.f.name)
-        except OSError:
-            pass
+                self._proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self._proc.kill()
+            self._f.flush()
+            self._f.seek(0)
+            for line in self._f:
+                c = [x.strip() for x in line.split(",")]
+                if len(c) < 7:
+                    continue
+                try:
+                    sm.append(float(c[0])); mx.append(float(c[1])); pw.append(float(c[2]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, c[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            self._f.close()
+            try:
+                os.unlink(self._f.name)
+            except OSError:
+                pass
+            out["how"] = "nvidia-smi -lms 1000 subprocess"
         if sm:
             out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), power_w_max=max(pw), reasons=sorted(reasons), samples=len(sm))
         return out
@@ -155,7 +207,7 @@ def run_reference_arm(args):
 
 def workload_config(args) -> dict:
     return {"workload": f"Stokes3D_FxU direct summation, Ns=Nt={args.n}, FP64 (BASELINE.json configs[2])", "kernel": "Stokes3D_FxU",
-            "n_sources": args.n, "n_targets": args.n, "parallelism": f"targets sharded x{args.gpus}, sources sharded + NCCL broadcast",
+            "n_sources": args.n, "n_targets": args.n, "parallelism": f"targets sharded x{args.gpus}, sources sharded + NCCL all-gather",
             "l2": f"no flush; source records streamed per step = {args.n * 48 / 1e6:.0f} MB vs 126 MB L2"
             + (" (inputs larger than L2)" if args.n * 48 > 126e6 else " (fits L2: compute-bound kernel, HBM traffic is not the limiter)")}
 
@@ -225,15 +277,18 @@ def run_b200_arm(args):
     for _ in range(args.warmup):
         step()
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    sampler = ClockSampler(local_rank) if (rank == 0 and not os.environ.get("SCTL_B200_BENCH_NO_SAMPLER")) else None
     l0 = capi.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    evs[0].record()
+    for i in range(args.steps):
         step()
-    e1.record()
+        evs[i + 1].record()
     barrier()
-    ms_step = allmax(e0.elapsed_time(e1) / args.steps)
+    ms_steps = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    if os.environ.get("SCTL_B200_BENCH_VERBOSE"):
+        print(f"[rank {rank}] per-step ms: {ms_steps}", file=sys.stderr, flush=True)
+    ms_step = allmax(evs[0].elapsed_time(evs[-1]) / args.steps)
     clocks = sampler.stop() if sampler else {}
     launches = int(allsum(capi.launch_count() - l0))
     value = float(n) * float(n) / (ms_step * 1e-3)

@@ -20,7 +20,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, kid, Nt, Ns, out_dir):
+def _worker(rank, world, port, kid, Nt, Ns, out_dir, mode):
     sys.path.insert(0, ROOT)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -42,7 +42,7 @@ def _worker(rank, world, port, kid, Nt, Ns, out_dir):
         return U
 
     T = lambda a: None if a is None else torch.from_numpy(a)
-    drv = ShardedDirectSum(KERNELS[kid](), evaluator=evaluator)
+    drv = ShardedDirectSum(KERNELS[kid](), evaluator=evaluator, mode=mode)
     U = torch.full((d["trg_dim"] * (t1 - t0),), 123.0, dtype=torch.float64)  # stale contents must be overwritten
     U = drv(U, T(Xt), T(Xs), T(Xn), T(F))
     U2 = drv(None, T(Xt), T(Xs), T(Xn), T(F), counts=[partition(Ns, r, world)[1] - partition(Ns, r, world)[0] for r in range(world)])
@@ -52,10 +52,11 @@ def _worker(rank, world, port, kid, Nt, Ns, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("kid,Nt,Ns", [(3, 101, 57), (4, 64, 33), (0, 7, 1)])
-def test_sharded_direct_sum_world2(tmp_path, port, kid, Nt, Ns):
+@pytest.mark.parametrize("kid,Nt,Ns,mode", [(3, 101, 57, "gather"), (4, 64, 34, "gather"), (0, 7, 1, "gather"), (4, 64, 33, "ring"), (3, 50, 58, "ring")])
+def test_sharded_direct_sum_world2(tmp_path, port, kid, Nt, Ns, mode):
+    """ragged blocks (chained broadcasts), even blocks (one all-gather), an empty block, and the ring mode"""
     world = 2
-    mp.spawn(_worker, args=(world, _free_port(), kid, Nt, Ns, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), kid, Nt, Ns, str(tmp_path), mode), nprocs=world, join=True)
     from sctl_b200 import capi, synth
 
     d = capi.kernel_dims(kid)
@@ -63,7 +64,7 @@ def test_sharded_direct_sum_world2(tmp_path, port, kid, Nt, Ns):
     want = port.eval(kid, Xt, Xs, Xn, F)
     got = np.concatenate([np.load(tmp_path / f"u{r}.npy") for r in range(world)])
     assert got.shape == want.shape
-    assert np.linalg.norm(got - want) <= 1e-14 * np.linalg.norm(want)
+    assert np.linalg.norm(got - want) <= 1e-13 * np.linalg.norm(want)
 
 
 def test_partition_formula():

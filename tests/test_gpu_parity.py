@@ -109,3 +109,15 @@ def test_launch_counter_moves():
     Xt, Xs, Xn, F = _problem(0, 10, 10, np.float64)
     KERNELS[0]().Eval(None, Xt, Xs, Xn, F)
     assert capi.launch_count() >= n0 + 2
+
+
+@pytest.mark.parametrize("kid,dt", [(3, np.float64), (1, np.float32)])
+def test_eval_all_gpus_flag(checker, kid, dt):
+    """SCTL_B200_ALL_GPUS: in-process target sharding over every visible device with the partition formula of
+    fmm-wrapper.txx:507 (falls back to one device when only one is visible); accumulate semantics are kept per shard."""
+    Xt, Xs, Xn, F = _problem(kid, 7001, 3000, dt)
+    K1 = capi.kernel_dims(kid)["trg_dim"]
+    U0 = synth.uniform(9, 0, 7001 * K1, dtype=dt)
+    want = checker.eval(kid, Xt, Xs, Xn, F, v_trg=U0.copy())
+    got = KERNELS[kid]().Eval(U0.copy(), Xt, Xs, Xn, F, all_gpus=True)
+    assert rel_l2(got, want) <= TOL[np.dtype(dt)]

@@ -373,10 +373,17 @@ def run_b200_arm(args):
 
 def main():
     args = parse_args()
+    # stdout carries exactly ONE JSON line: everything libraries print while we run (e.g. "NCCL version ..." from the first
+    # communicator) is sent to stderr, and print() below writes to the saved descriptor.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if args.impl == "reference":
         run_reference_arm(args)
     else:
         run_b200_arm(args)
+    real_stdout.flush()
 
 
 if __name__ == "__main__":

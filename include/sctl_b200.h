@@ -103,6 +103,20 @@ SCTL_B200_API int sctl_b200_kernel_matrix(int kernel_id, int dtype, int64_t Nt, 
 SCTL_B200_API int sctl_b200_kernel_matrix_async(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* d_r_trg, const void* d_r_src,
                                   const void* d_n_src, void* d_M, int digits, unsigned flags, void* cuda_stream);
 
+/* Batched small-block KernelMatrix — ONE launch for what the reference's BoundaryIntegralOp::SetupNear does with one
+ * KernelMatrix call per element (boundary_integral.txx:946-1008). Block b couples targets [trg_dsp[b], trg_dsp[b+1]) of r_trg
+ * (and n_trg) with sources [src_dsp[b], src_dsp[b+1]) of r_src / n_src / src_wts — the reference's near_elem_dsp /
+ * elem_nds_dsp_far displacements, in POINTS — and is written row-major at M + M_dsp[b] (elements) as a
+ * (Ns_b*K0) x (Nt_b*K1out) matrix. The three displacement arrays are always HOST pointers (trg_dsp, src_dsp: nbatch+1
+ * entries; M_dsp: nbatch). Optional fused epilogues of that call site:
+ *   src_wts != NULL : row (s,k0) is multiplied by src_wts[s]                                   (boundary_integral.txx:990-997)
+ *   n_trg   != NULL : K1out = K1/3 and M[.][t*K1out+k] = sum_l K[.][k*3+l] * n_trg[t*3+l]      (boundary_integral.txx:968-984;
+ *                     needs TrgDim % 3 == 0: Laplace3D_FxdU, Stokes3D_FxT); otherwise K1out = K1.
+ * Entries of M not covered by any block are left untouched. */
+SCTL_B200_API int sctl_b200_kernel_matrix_batch(int kernel_id, int dtype, int64_t nbatch, const int64_t* trg_dsp, const int64_t* src_dsp,
+                                  const int64_t* M_dsp, const void* r_trg, const void* r_src, const void* n_src, const void* src_wts,
+                                  const void* n_trg, void* M, int64_t M_len, int digits, unsigned flags);
+
 /* Device-resident Vector storage (north_star: "device-resident Vector buffers"): raw device memory on the
  * current device, usable with SCTL_B200_DEVICE_PTRS / *_async. */
 SCTL_B200_API int sctl_b200_buf_create(void** d_ptr, int dtype, int64_t n);

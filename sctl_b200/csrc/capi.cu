@@ -396,6 +396,86 @@ static int kmat_host(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const voi
 }
 
 // ------------------------------------------------------------------------------------------------
+// batched small-block KernelMatrix (one launch for all blocks)
+// ------------------------------------------------------------------------------------------------
+static int kmat_batch_impl(int kernel_id, int dtype, int64_t nbatch, const int64_t* trg_dsp, const int64_t* src_dsp, const int64_t* M_dsp,
+                           const void* r_trg, const void* r_src, const void* n_src, const void* src_wts, const void* n_trg, void* M, int64_t M_len,
+                           int digits, bool device_ptrs) {
+  DevCtx* c = nullptr;
+  int rc = get_ctx(&c);
+  if (rc) return rc;
+  const KernelInfo& ki = KINFO[kernel_id];
+  const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
+  const size_t esz = elem_size(dtype);
+  const int dotn = n_trg ? 1 : 0;
+  const int newton = newton_level(dtype, digits);
+  if (dotn && !E.kmat_batch[1][newton]) return set_error(SCTL_B200_ERR_ARG, "target-normal contraction needs TrgDim %% 3 == 0 (%s has %d)", ki.name, ki.trg_dim);
+  const int k1out = dotn ? ki.trg_dim / 3 : ki.trg_dim;
+  // validate the CSR description and build the CTA prefix sum (host side, O(nbatch))
+  std::vector<long long> desc(4 * (size_t)nbatch + 3);
+  long long* h_trg = desc.data();
+  long long* h_src = h_trg + nbatch + 1;
+  long long* h_M = h_src + nbatch + 1;
+  long long* h_cta = h_M + nbatch;
+  h_cta[0] = 0;
+  for (int64_t b = 0; b <= nbatch; b++) {
+    h_trg[b] = trg_dsp[b];
+    h_src[b] = src_dsp[b];
+  }
+  if (trg_dsp[0] < 0 || src_dsp[0] < 0) return set_error(SCTL_B200_ERR_ARG, "negative displacement");
+  for (int64_t b = 0; b < nbatch; b++) {
+    const long long nt = trg_dsp[b + 1] - trg_dsp[b], ns = src_dsp[b + 1] - src_dsp[b];
+    if (nt < 0 || ns < 0) return set_error(SCTL_B200_ERR_ARG, "block %lld: displacements must be non-decreasing", (long long)b);
+    const long long len = ns * ki.src_dim * nt * k1out;
+    if (M_dsp[b] < 0 || M_dsp[b] + len > M_len) return set_error(SCTL_B200_ERR_ARG, "block %lld does not fit in M (offset %lld + %lld > %lld)", (long long)b, (long long)M_dsp[b], len, (long long)M_len);
+    h_M[b] = M_dsp[b];
+    const long long ctas = (nt && ns) ? ((nt + KMAT_THREADS - 1) / KMAT_THREADS) * ((ns + KMAT_SB - 1) / KMAT_SB) : 0;
+    h_cta[b + 1] = h_cta[b] + ctas;
+  }
+  const long long n_ctas = h_cta[nbatch];
+  if (n_ctas == 0) return 0;
+  const int64_t Nt_all = trg_dsp[nbatch], Ns_all = src_dsp[nbatch];
+  cudaStream_t st = c->stream;
+  DevAlloc d_desc, d_rt, d_rs, d_ns, d_w, d_nt, d_M;
+  if ((rc = d_desc.alloc(desc.size() * sizeof(long long), st))) return rc;
+  CU_TRY(cudaMemcpyAsync(d_desc.p, desc.data(), desc.size() * sizeof(long long), cudaMemcpyHostToDevice, st));
+  const void *p_rt = r_trg, *p_rs = r_src, *p_ns = n_src, *p_w = src_wts, *p_nt = n_trg;
+  void* p_M = M;
+  if (!device_ptrs) {
+    auto up = [&](DevAlloc& d, const void* h, size_t bytes, const void** out) -> int {
+      if (!h || !bytes) {
+        *out = nullptr;
+        return 0;
+      }
+      int r = d.alloc(bytes, st);
+      if (r) return r;
+      cudaError_t e = cudaMemcpyAsync(d.p, h, bytes, cudaMemcpyHostToDevice, st);
+      if (e != cudaSuccess) return cuda_error(e, "cudaMemcpyAsync");
+      *out = d.p;
+      return 0;
+    };
+    if ((rc = up(d_rt, r_trg, (size_t)Nt_all * 3 * esz, &p_rt)) || (rc = up(d_rs, r_src, (size_t)Ns_all * 3 * esz, &p_rs)) ||
+        (rc = up(d_ns, ki.normal_dim ? n_src : nullptr, (size_t)Ns_all * ki.normal_dim * esz, &p_ns)) ||
+        (rc = up(d_w, src_wts, (size_t)Ns_all * esz, &p_w)) || (rc = up(d_nt, n_trg, (size_t)Nt_all * 3 * esz, &p_nt)))
+      return rc;
+    if ((rc = d_M.alloc((size_t)M_len * esz, st))) return rc;
+    // entries of M that no block covers keep the caller's values: stage the caller's buffer in first
+    CU_TRY(cudaMemcpyAsync(d_M.p, M, (size_t)M_len * esz, cudaMemcpyHostToDevice, st));
+    p_M = d_M.p;
+  }
+  KmatBatchDesc D{};
+  D.trg_dsp = (const long long*)d_desc.p;
+  D.src_dsp = D.trg_dsp + nbatch + 1;
+  D.M_dsp = D.src_dsp + nbatch + 1;
+  D.cta_dsp = D.M_dsp + nbatch;
+  D.nbatch = nbatch;
+  CU_TRY(E.kmat_batch[dotn][newton](p_rt, p_rs, p_ns, p_w, p_nt, p_M, D, n_ctas, kernel_scale(kernel_id), st));
+  if (!device_ptrs) CU_TRY(cudaMemcpyAsync(M, p_M, (size_t)M_len * esz, cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
 // Device-resident particle context: the GPU-aware counterpart of ParticleFMM's registry + EvalDirect
 // (reference: fmm-wrapper.txx:297-479 registry, :490-562 EvalDirect). Coordinates, normals, densities and
 // the packed source records stay in HBM between calls; records are re-packed only when the coordinates or
@@ -788,6 +868,22 @@ int sctl_b200_kernel_matrix_async(int kernel_id, int dtype, int64_t Nt, int64_t 
   DevCtx* c = nullptr;
   if ((rc = get_ctx(&c))) return rc;
   return kmat_device(kernel_id, dtype, Nt, Ns, d_r_trg, d_r_src, d_n_src, d_M, digits, (cudaStream_t)cuda_stream);
+}
+
+int sctl_b200_kernel_matrix_batch(int kernel_id, int dtype, int64_t nbatch, const int64_t* trg_dsp, const int64_t* src_dsp, const int64_t* M_dsp,
+                                  const void* r_trg, const void* r_src, const void* n_src, const void* src_wts, const void* n_trg, void* M,
+                                  int64_t M_len, int digits, unsigned flags) {
+  int rc = check_common(kernel_id, dtype, 0, 0);
+  if (rc) return rc;
+  if (nbatch < 0 || M_len < 0) return set_error(SCTL_B200_ERR_ARG, "negative size");
+  if (nbatch == 0) return 0;
+  if (!trg_dsp || !src_dsp || !M_dsp) return set_error(SCTL_B200_ERR_ARG, "null block description");
+  const KernelInfo& ki = KINFO[kernel_id];
+  if (trg_dsp[nbatch] > 0 && src_dsp[nbatch] > 0 && (!r_trg || !r_src || !M || (ki.normal_dim && !n_src)))
+    return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if (flags & SCTL_B200_ALL_GPUS) return set_error(SCTL_B200_ERR_ARG, "SCTL_B200_ALL_GPUS is not supported for kernel_matrix_batch");
+  return kmat_batch_impl(kernel_id, dtype, nbatch, trg_dsp, src_dsp, M_dsp, r_trg, r_src, n_src, src_wts, n_trg, M, M_len, digits,
+                         (flags & SCTL_B200_DEVICE_PTRS) != 0);
 }
 
 int sctl_b200_buf_create(void** d_ptr, int dtype, int64_t n) {

@@ -82,6 +82,31 @@ cudaError_t kmat_t(const void* r_trg, const void* r_src, const void* n_src, void
   return cudaGetLastError();
 }
 
+template <class Ker, int NEWTON, bool DOTN>
+cudaError_t kmat_batch_t(const void* r_trg, const void* r_src, const void* n_src, const void* src_wts, const void* n_trg, void* M,
+                         const KmatBatchDesc& D, long long n_ctas, double scale, cudaStream_t st) {
+  // 1-D grid; walk it in slabs of 2^30 CTAs (far beyond any real batch, but the limit is 2^31-1)
+  for (long long c0 = 0; c0 < n_ctas; c0 += (1ll << 30)) {
+    const long long n = n_ctas - c0 < (1ll << 30) ? n_ctas - c0 : (1ll << 30);
+    kmat_batch_kernel<Ker, Real, NEWTON, DOTN><<<(unsigned)n, KMAT_THREADS, 0, st>>>((const Real*)r_trg, (const Real*)r_src, (const Real*)n_src,
+                                                                                  (const Real*)src_wts, (const Real*)n_trg, (Real*)M, D, c0, (Real)scale);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
+}
+template <class Ker, bool HAS> struct KmatDotN {
+  static void fill(EvalEntry& e) {
+    e.kmat_batch[1][0] = kmat_batch_t<Ker, 0, true>;
+    e.kmat_batch[1][1] = kmat_batch_t<Ker, 1, true>;
+    e.kmat_batch[1][2] = kmat_batch_t<Ker, IS_F32 ? 1 : 2, true>;
+  }
+};
+template <class Ker> struct KmatDotN<Ker, false> {
+  static void fill(EvalEntry& e) { e.kmat_batch[1][0] = e.kmat_batch[1][1] = e.kmat_batch[1][2] = nullptr; }
+};
+
 template <class Ker, int ID>
 EvalEntry make_entry() {
   EvalEntry e{};
@@ -112,6 +137,10 @@ EvalEntry make_entry() {
   e.kmat[0] = kmat_t<Ker, 0>;
   e.kmat[1] = kmat_t<Ker, 1>;
   e.kmat[2] = kmat_t<Ker, IS_F32 ? 1 : 2>;
+  e.kmat_batch[0][0] = kmat_batch_t<Ker, 0, false>;
+  e.kmat_batch[0][1] = kmat_batch_t<Ker, 1, false>;
+  e.kmat_batch[0][2] = kmat_batch_t<Ker, IS_F32 ? 1 : 2, false>;
+  KmatDotN<Ker, Ker::K1 % 3 == 0>::fill(e);
   return e;
   }
 }

@@ -21,31 +21,45 @@ constexpr int KMAT_WARPS = 4;
 constexpr int KMAT_THREADS = KMAT_WARPS * 32;
 constexpr int KMAT_SB = 32;  // sources per CTA
 
-template <class Ker, class Real, int NEWTON>
-__global__ void __launch_bounds__(KMAT_THREADS) kmat_kernel(const Real* __restrict__ r_trg, const Real* __restrict__ r_src,
-                                                            const Real* __restrict__ n_src, Real* __restrict__ M, long long Nt,
-                                                            long long Ns, Real scale) {
+// One CTA's share of one dense block: targets [tile_x*128, +128) x sources [slab_y*32, +32) of an Nt x Ns problem.
+//   DOTN = false: M[(s*K0+k0)*ld + t*K1+k1]   = w_s * scale * K[k0][k1]                  (KernelMatrix, generic-kernel.txx:284;
+//                                                 w_s = src_wts[s] or 1: the row scaling of boundary_integral.txx:990-997)
+//   DOTN = true : M[(s*K0+k0)*ld + t*K1'+k1'] = w_s * scale * sum_l K[k0][k1'*3+l] * n_trg[t][l],   K1' = K1/3
+//                                                 (the target-normal contraction of boundary_integral.txx:968-984)
+// ld = Nt*K1 (or Nt*K1'). slab: KMAT_WARPS * K0 * 32*K1OUT Reals of shared memory.
+template <class Ker, class Real, int NEWTON, bool DOTN>
+__device__ __forceinline__ void kmat_block(const Real* __restrict__ r_trg, const Real* __restrict__ r_src, const Real* __restrict__ n_src,
+                                           const Real* __restrict__ src_wts, const Real* __restrict__ n_trg, Real* __restrict__ M, long long Nt,
+                                           long long Ns, long long tile_x, long long slab_y, Real scale, Real* slab_all) {
   constexpr int K0 = Ker::K0, K1 = Ker::K1, ND = Ker::ND;
-  constexpr int SPAN = 32 * K1;  // elements per row owned by one warp
-  __shared__ Real slab[KMAT_WARPS][K0][SPAN];
+  constexpr int K1OUT = DOTN ? K1 / 3 : K1;
+  constexpr int SPAN = 32 * K1OUT;  // elements per row owned by one warp
 
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const long long t0 = ((long long)blockIdx.x * KMAT_WARPS + warp) * 32;  // first target of this warp
-  if (t0 >= Nt) return;                                                   // whole warp out of range (no CTA-wide sync below)
+  Real(*slab)[SPAN] = reinterpret_cast<Real(*)[SPAN]>(slab_all + (size_t)warp * K0 * SPAN);
+  const long long t0 = (tile_x * KMAT_WARPS + warp) * 32;  // first target of this warp
+  if (t0 >= Nt) return;                                    // whole warp out of range (no CTA-wide sync below)
   const long long t = t0 + lane;
   const long long tc = t < Nt ? t : Nt - 1;
   const Real xt = r_trg[tc * 3 + 0], yt = r_trg[tc * 3 + 1], zt = r_trg[tc * 3 + 2];
-  const long long span_valid = min((long long)SPAN, (Nt - t0) * K1);  // valid elements of this warp's span
-  const long long ld = Nt * K1;
+  Real nt[3] = {0, 0, 0};
+  if (DOTN) {
+    nt[0] = n_trg[tc * 3 + 0];
+    nt[1] = n_trg[tc * 3 + 1];
+    nt[2] = n_trg[tc * 3 + 2];
+  }
+  const long long span_valid = min((long long)SPAN, (Nt - t0) * K1OUT);  // valid elements of this warp's span
+  const long long ld = Nt * K1OUT;
 
-  const long long s_begin = (long long)blockIdx.y * KMAT_SB;
+  const long long s_begin = slab_y * KMAT_SB;
   const long long s_end = min(Ns, s_begin + KMAT_SB);
   for (long long s = s_begin; s < s_end; s++) {
     const Real xs = __ldg(r_src + s * 3 + 0), ys = __ldg(r_src + s * 3 + 1), zs = __ldg(r_src + s * 3 + 2);
     Real n[3] = {0, 0, 0};
 #pragma unroll
     for (int i = 0; i < ND; i++) n[i] = __ldg(n_src + s * ND + i);
+    const Real w = src_wts ? __ldg(src_wts + s) * scale : scale;
     const Real dx = xt - xs, dy = yt - ys, dz = zt - zs;
     Real r2 = dx * dx;
     r2 = fma(dy, dy, r2);
@@ -53,24 +67,91 @@ __global__ void __launch_bounds__(KMAT_THREADS) kmat_kernel(const Real* __restri
     const Real rinv = rsqrt_masked<NEWTON>(r2);
     Real u[K0][K1];
     Ker::matrix(u, dx, dy, dz, rinv, n);
-
-    __syncwarp();  // previous iteration's reads of the slab are complete
+    Real v[K0][K1OUT];
 #pragma unroll
     for (int k0 = 0; k0 < K0; k0++) {
 #pragma unroll
-      for (int k1 = 0; k1 < K1; k1++) slab[warp][k0][lane * K1 + k1] = u[k0][k1] * scale;
+      for (int k1 = 0; k1 < K1OUT; k1++) {
+        if (DOTN) {
+          Real a = u[k0][k1 * 3 + 0] * nt[0];
+          a = fma(u[k0][k1 * 3 + 1], nt[1], a);
+          a = fma(u[k0][k1 * 3 + 2], nt[2], a);
+          v[k0][k1] = a * w;
+        } else {
+          v[k0][k1] = u[k0][k1] * w;
+        }
+      }
     }
-    __syncwarp();
-    Real* row = M + (size_t)(s * K0) * (size_t)ld + (size_t)t0 * K1;
+    Real* row = M + (size_t)(s * K0) * (size_t)ld + (size_t)t0 * K1OUT;
+    if (K1OUT == 1) {
+      // a lane's element IS its position in the row: store directly, no transpose needed
 #pragma unroll
-    for (int k0 = 0; k0 < K0; k0++) {
+      for (int k0 = 0; k0 < K0; k0++) {
+        if (lane < span_valid) row[(size_t)k0 * (size_t)ld + lane] = v[k0][0];
+      }
+    } else {
+      __syncwarp();  // previous iteration's reads of the slab are complete
 #pragma unroll
-      for (int j = 0; j < K1; j++) {
-        const int e = j * 32 + lane;
-        if (e < span_valid) row[(size_t)k0 * (size_t)ld + e] = slab[warp][k0][e];
+      for (int k0 = 0; k0 < K0; k0++) {
+#pragma unroll
+        for (int k1 = 0; k1 < K1OUT; k1++) slab[k0][lane * K1OUT + k1] = v[k0][k1];
+      }
+      __syncwarp();
+#pragma unroll
+      for (int k0 = 0; k0 < K0; k0++) {
+#pragma unroll
+        for (int j = 0; j < K1OUT; j++) {
+          const int e = j * 32 + lane;
+          if (e < span_valid) row[(size_t)k0 * (size_t)ld + e] = slab[k0][e];
+        }
       }
     }
   }
+}
+
+template <class Ker, class Real, int NEWTON>
+__global__ void __launch_bounds__(KMAT_THREADS) kmat_kernel(const Real* __restrict__ r_trg, const Real* __restrict__ r_src,
+                                                            const Real* __restrict__ n_src, Real* __restrict__ M, long long Nt,
+                                                            long long Ns, Real scale) {
+  __shared__ Real slab[KMAT_WARPS * Ker::K0 * 32 * Ker::K1];
+  kmat_block<Ker, Real, NEWTON, false>(r_trg, r_src, n_src, nullptr, nullptr, M, Nt, Ns, blockIdx.x, blockIdx.y, scale, slab);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Batched small-block mode: the reference's BoundaryIntegralOp::SetupNear calls KernelMatrix once per
+// element on (that element's far-field nodes) x (its near targets) — thousands of tiny blocks per setup
+// (boundary_integral.txx:946-1008). Here ALL blocks are one launch: blocks are described CSR-style by point
+// displacements into the concatenated coordinate arrays (exactly the reference's near_elem_dsp / elem_nds_dsp_far),
+// each CTA finds its block by binary search in the prefix sum of CTAs per block.
+// ---------------------------------------------------------------------------------------------
+struct KmatBatchDesc {
+  const long long* trg_dsp;  // [nbatch+1] points
+  const long long* src_dsp;  // [nbatch+1] points
+  const long long* M_dsp;    // [nbatch]   element offset of block b in M
+  const long long* cta_dsp;  // [nbatch+1] prefix sum of CTAs per block
+  long long nbatch;
+};
+
+template <class Ker, class Real, int NEWTON, bool DOTN>
+__global__ void __launch_bounds__(KMAT_THREADS) kmat_batch_kernel(const Real* __restrict__ r_trg, const Real* __restrict__ r_src,
+                                                                  const Real* __restrict__ n_src, const Real* __restrict__ src_wts,
+                                                                  const Real* __restrict__ n_trg, Real* __restrict__ M, KmatBatchDesc D,
+                                                                  long long cta0, Real scale) {
+  __shared__ Real slab[KMAT_WARPS * Ker::K0 * 32 * (DOTN ? Ker::K1 / 3 : Ker::K1)];
+  const long long cta = cta0 + blockIdx.x;
+  long long lo = 0, hi = D.nbatch;  // block b with cta_dsp[b] <= cta < cta_dsp[b+1]
+  while (hi - lo > 1) {
+    const long long mid = (lo + hi) >> 1;
+    if (D.cta_dsp[mid] <= cta) lo = mid; else hi = mid;
+  }
+  const long long b = lo;
+  const long long Nt = D.trg_dsp[b + 1] - D.trg_dsp[b];
+  const long long Ns = D.src_dsp[b + 1] - D.src_dsp[b];
+  const long long ntx = (Nt + KMAT_THREADS - 1) / KMAT_THREADS;
+  const long long c = cta - D.cta_dsp[b];
+  const long long so = D.src_dsp[b], to = D.trg_dsp[b];
+  kmat_block<Ker, Real, NEWTON, DOTN>(r_trg + to * 3, r_src + so * 3, Ker::ND ? n_src + so * Ker::ND : nullptr, src_wts ? src_wts + so : nullptr,
+                                      DOTN ? n_trg + to * 3 : nullptr, M + D.M_dsp[b], Nt, Ns, c % ntx, c / ntx, scale, slab);
 }
 
 }  // namespace sctl_b200

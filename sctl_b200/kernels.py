@@ -151,6 +151,49 @@ class GenericKernel:
         return M
 
 
+    # --- batched small-block KernelMatrix (the per-element calls of BoundaryIntegralOp::SetupNear, boundary_integral.txx:946-1008)
+    def KernelMatrixBatch(self, trg_dsp, src_dsp, r_trg, r_src, n_src=None, src_wts=None, n_trg=None, digits: int = -1, out=None, M_dsp=None):
+        """All blocks in ONE launch. Block b = targets [trg_dsp[b], trg_dsp[b+1]) x sources [src_dsp[b], src_dsp[b+1]) (point
+        displacements, like the reference's near_elem_dsp / elem_nds_dsp_far). Returns (M, M_dsp): the blocks, each row-major
+        (Ns_b*SrcDim) x (Nt_b*K1out), concatenated in a flat array at element offsets M_dsp. src_wts scales row (s, k0) by
+        src_wts[s]; n_trg contracts every triplet of target components with the target normal (K1out = TrgDim/3)."""
+        K0, K1 = self.SrcDim(), self.TrgDim()
+        trg_dsp = np.ascontiguousarray(trg_dsp, dtype=np.int64)
+        src_dsp = np.ascontiguousarray(src_dsp, dtype=np.int64)
+        nb = trg_dsp.size - 1
+        if nb < 0 or src_dsp.size != nb + 1:
+            raise ValueError("trg_dsp and src_dsp must both hold nbatch+1 displacements")
+        k1out = K1 // 3 if n_trg is not None else K1
+        if n_trg is not None and K1 % 3:
+            raise ValueError("target-normal contraction needs TrgDim % 3 == 0")
+        sizes = np.diff(src_dsp) * K0 * np.diff(trg_dsp) * k1out
+        if M_dsp is None:
+            M_dsp = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.int64) if nb else np.zeros(0, np.int64)
+        M_dsp = np.ascontiguousarray(M_dsp, dtype=np.int64)
+        M_len = int((M_dsp + sizes).max()) if nb else 0
+        i64p = lambda a: a.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))
+        if _is_torch(r_trg):
+            import torch
+
+            tdt = {torch.float32: capi.F32, torch.float64: capi.F64}[r_trg.dtype]
+            M = out if out is not None else torch.zeros(M_len, dtype=r_trg.dtype, device=r_trg.device)
+            p = lambda a: None if a is None or a.numel() == 0 else ctypes.c_void_p(a.data_ptr())
+            with torch.cuda.device(r_trg.device):
+                torch.cuda.current_stream().synchronize()  # the library runs the batch on its own stream
+                capi.check(capi.lib().sctl_b200_kernel_matrix_batch(self.KERNEL_ID, tdt, nb, i64p(trg_dsp), i64p(src_dsp), i64p(M_dsp), p(r_trg), p(r_src),
+                                                                    p(n_src) if self.NormalDim() else None, p(src_wts), p(n_trg), p(M), M.numel(), digits,
+                                                                    capi.DEVICE_PTRS))
+            return M, M_dsp
+        dt = np.dtype(r_trg.dtype)
+        c = lambda a: None if a is None else np.ascontiguousarray(a, dtype=dt).reshape(-1)
+        r_trg, r_src, n_src, src_wts, n_trg = c(r_trg), c(r_src), c(n_src), c(src_wts), c(n_trg)
+        M = out if out is not None else np.zeros(M_len, dtype=dt)
+        capi.check(capi.lib().sctl_b200_kernel_matrix_batch(self.KERNEL_ID, _NP2DT[dt], nb, i64p(trg_dsp), i64p(src_dsp), i64p(M_dsp), self._np_ptr(r_trg),
+                                                            self._np_ptr(r_src), self._np_ptr(n_src) if self.NormalDim() else None, self._np_ptr(src_wts),
+                                                            self._np_ptr(n_trg), self._np_ptr(M), M.size, digits, 0))
+        return M, M_dsp
+
+
 class Laplace3D_FxU(GenericKernel):
     KERNEL_ID = 0
 

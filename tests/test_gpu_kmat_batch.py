@@ -73,7 +73,7 @@ def test_batch_target_normal_contraction(checker, kid):
     for b, w in enumerate(want):
         if w.size:
             assert rel_l2(M[M_dsp[b]:M_dsp[b] + w.size], w) <= 1e-12, b
-    with pytest.raises(capi.SctlB200Error):  # Stokes FxU has TrgDim 3 -> fine; Laplace FxU (TrgDim 1) cannot be contracted
+    with pytest.raises(ValueError):  # Laplace FxU (TrgDim 1) cannot be contracted with a target normal
         KERNELS[0]().KernelMatrixBatch(trg_dsp, src_dsp, Xt, Xs, None, n_trg=Nt_n)
 
 

@@ -143,6 +143,12 @@ SCTL_B200_API int sctl_b200_fmm_delete_trg(void* fmm, const char* name);        
 SCTL_B200_API int sctl_b200_fmm_set_src_coord(void* fmm, const char* name, int64_t Ns, const void* r_src, const void* n_src, unsigned flags); /* :444 */
 SCTL_B200_API int sctl_b200_fmm_set_src_density(void* fmm, const char* name, int64_t n, const void* v_src, unsigned flags);                  /* :462 */
 SCTL_B200_API int sctl_b200_fmm_set_trg_coord(void* fmm, const char* name, int64_t Nt, const void* r_trg, unsigned flags);                   /* :467 */
+/* Fused glue of BoundaryIntegralOp::ComputeFarField (optional; n == 0 removes it again):
+ *   weights : the density of source `name` is multiplied by wts[s] when records are packed   (boundary_integral.txx:1036-1051)
+ *   normals : eval_direct returns U[t*K1'+k] = sum_l Usum[(t*K1'+k)*3+l] * n_trg[t*3+l], K1' = TrgDim/3   (:1060-1071) */
+SCTL_B200_API int sctl_b200_fmm_set_src_weights(void* fmm, const char* name, int64_t n, const void* wts, unsigned flags);
+SCTL_B200_API int sctl_b200_fmm_set_trg_normal(void* fmm, const char* name, int64_t n, const void* n_trg, unsigned flags);
+/* Nt and the number of values per target that eval_direct returns (TrgDim, or TrgDim/3 with target normals) */
 SCTL_B200_API int sctl_b200_fmm_trg_count(void* fmm, const char* name, int64_t* Nt, int* trg_dim);
 SCTL_B200_API int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t n, unsigned flags);                            /* :490 */
 

@@ -83,6 +83,17 @@ template <class Real, sctl::Integer DIM = 3> class ParticleFMM {
     sctl_b200_shim::check(sctl_b200_fmm_set_trg_coord(h_, name.c_str(), (int64_t)Nt, sctl_b200_shim::cptr(trg_coord), 0u), "sctl_b200_fmm_set_trg_coord");
   }
 
+  // Extensions (not in the reference's ParticleFMM): the glue BoundaryIntegralOp::ComputeFarField does on the host around
+  // fmm.Eval, fused on the device. Weights scale the density when records are packed (boundary_integral.txx:1036-1051);
+  // target normals make Eval return TrgDim/3 values per target, the component triplets dotted with the normal (:1060-1071).
+  void SetSrcWeights(const std::string& name, const sctl::Vector<Real>& wts) {
+    sctl_b200_shim::check(sctl_b200_fmm_set_src_weights(h_, name.c_str(), (int64_t)wts.Dim(), sctl_b200_shim::cptr(wts), 0u), "sctl_b200_fmm_set_src_weights");
+  }
+  void SetTrgNormal(const std::string& name, const sctl::Vector<Real>& trg_normal) {
+    sctl_b200_shim::check(sctl_b200_fmm_set_trg_normal(h_, name.c_str(), (int64_t)trg_normal.Dim(), sctl_b200_shim::cptr(trg_normal), 0u),
+                          "sctl_b200_fmm_set_trg_normal");
+  }
+
   void Eval(sctl::Vector<Real>& U, const std::string& trg_name) const { EvalDirect(U, trg_name); }
   void EvalDirect(sctl::Vector<Real>& U, const std::string& trg_name) const {
     int64_t Nt = 0;

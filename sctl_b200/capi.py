@@ -43,6 +43,8 @@ SYMBOLS = {
     "sctl_b200_fmm_set_src_coord": (c_int, [c_void_p, c_char_p, c_int64, c_void_p, c_void_p, c_uint]),
     "sctl_b200_fmm_set_src_density": (c_int, [c_void_p, c_char_p, c_int64, c_void_p, c_uint]),
     "sctl_b200_fmm_set_trg_coord": (c_int, [c_void_p, c_char_p, c_int64, c_void_p, c_uint]),
+    "sctl_b200_fmm_set_src_weights": (c_int, [c_void_p, c_char_p, c_int64, c_void_p, c_uint]),
+    "sctl_b200_fmm_set_trg_normal": (c_int, [c_void_p, c_char_p, c_int64, c_void_p, c_uint]),
     "sctl_b200_fmm_trg_count": (c_int, [c_void_p, c_char_p, POINTER(c_int64), POINTER(c_int)]),
     "sctl_b200_fmm_eval_direct": (c_int, [c_void_p, c_char_p, c_void_p, c_int64, c_uint]),
     "sctl_b200_device_count": (c_int, [POINTER(c_int)]),

@@ -192,10 +192,11 @@ static EvalPlan make_plan(const EvalEntry& E, int dtype, int64_t Nt, int64_t Ns,
 
 // pack: AoS (r_src, n_src, v_src) -> tile-padded source records in `rec` (device). Ns_pad records are written.
 static int64_t padded_sources(int64_t Ns) { return (Ns + EVAL_TILE - 1) / EVAL_TILE * EVAL_TILE; }
-static int pack_device(int kernel_id, int dtype, int64_t Ns, const void* r_src, const void* n_src, const void* v_src, void* rec, cudaStream_t st) {
+static int pack_device(int kernel_id, int dtype, int64_t Ns, const void* r_src, const void* n_src, const void* v_src, const void* src_wts, void* rec,
+                       cudaStream_t st) {
   const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
   if (Ns == 0) return 0;
-  CU_TRY(E.pack(r_src, n_src, v_src, rec, Ns, padded_sources(Ns), st));
+  CU_TRY(E.pack(r_src, n_src, v_src, src_wts, rec, Ns, padded_sources(Ns), st));
   return 0;
 }
 
@@ -246,7 +247,7 @@ static int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const v
   int rc = rec.alloc((size_t)padded_sources(Ns) * E.rec_len * esz, st);
   if (rc) return rc;
   if (ev) CU_TRY(cudaEventRecord(ev[0], st));
-  if ((rc = pack_device(kernel_id, dtype, Ns, r_src, n_src, v_src, rec.p, st))) return rc;
+  if ((rc = pack_device(kernel_id, dtype, Ns, r_src, n_src, v_src, nullptr, rec.p, st))) return rc;
   if (ev) CU_TRY(cudaEventRecord(ev[1], st));
   return eval_packed_device(kernel_id, dtype, Nt, Ns, r_trg, rec.p, v_trg, digits, accumulate, st, sms, ev ? ev + 2 : nullptr);
 }
@@ -507,13 +508,15 @@ struct FmmSrc {
   int src_dim = 0, normal_dim = 0;
   int64_t Ns = 0;    // from the coordinates
   int64_t n_den = 0; // elements of the density last set
-  DevBuf X, Xn, F;
-  unsigned long long version = 0;  // bumped by SetSrcCoord / SetSrcDensity
+  DevBuf X, Xn, F, W;
+  int64_t n_wts = 0;  // 0 = no quadrature weights, else must equal Ns
+  unsigned long long version = 0;  // bumped by SetSrcCoord / SetSrcDensity / SetSrcWeights
 };
 struct FmmTrg {
   int trg_dim = 0;
   int64_t Nt = 0;
-  DevBuf X, U;
+  int64_t n_nrm = 0;  // 0 = no target-normal contraction, else must equal Nt*3
+  DevBuf X, U, Xn, Ufull;
 };
 struct FmmS2T {
   int kernel_id = -1;
@@ -730,6 +733,35 @@ int sctl_b200_fmm_set_trg_coord(void* fmm, const char* name, int64_t Nt, const v
   t->Nt = Nt;
   return 0;
 }
+// Optional far-field quadrature weights of a source: the density is multiplied by wts[s] when the records are packed
+// (BoundaryIntegralOp::ComputeFarField scales F_far by wts_far on the host before SetSrcDensity, boundary_integral.txx:1036-1051).
+// n == 0 removes the weights.
+int sctl_b200_fmm_set_src_weights(void* fmm, const char* name, int64_t n, const void* wts, unsigned flags) {
+  FMM_ENTER(fmm);
+  FmmSrc* s = name ? C->find_src(name) : nullptr;
+  if (!s) return set_error(SCTL_B200_ERR_ARG, "Source name does not exist.");
+  if (n < 0 || (n > 0 && !wts)) return set_error(SCTL_B200_ERR_ARG, "bad source weights");
+  int rc = fmm_upload(s->W, wts, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream);
+  if (rc) return rc;
+  CU_TRY(cudaStreamSynchronize(c->stream));
+  s->n_wts = n;
+  s->version++;
+  return 0;
+}
+// Optional target normals: eval_direct then returns U[t*K1'+k] = sum_l Ufull[(t*K1'+k)*3+l] * n_trg[t*3+l] with K1' = TrgDim/3
+// (the trg_normal_dot_prod_ branch of ComputeFarField, boundary_integral.txx:1060-1071). n == 0 removes them.
+int sctl_b200_fmm_set_trg_normal(void* fmm, const char* name, int64_t n, const void* n_trg, unsigned flags) {
+  FMM_ENTER(fmm);
+  FmmTrg* t = name ? C->find_trg(name) : nullptr;
+  if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
+  if (n < 0 || (n > 0 && !n_trg)) return set_error(SCTL_B200_ERR_ARG, "bad target normals");
+  if (n > 0 && t->trg_dim % 3) return set_error(SCTL_B200_ERR_ARG, "target-normal contraction needs TrgDim %% 3 == 0 (target '%s' has %d)", name, t->trg_dim);
+  int rc = fmm_upload(t->Xn, n_trg, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream);
+  if (rc) return rc;
+  CU_TRY(cudaStreamSynchronize(c->stream));
+  t->n_nrm = n;
+  return 0;
+}
 int sctl_b200_fmm_trg_count(void* fmm, const char* name, int64_t* Nt, int* trg_dim) {
   if (!fmm || !name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
   FmmCtx* C = (FmmCtx*)fmm;
@@ -737,7 +769,7 @@ int sctl_b200_fmm_trg_count(void* fmm, const char* name, int64_t* Nt, int* trg_d
   FmmTrg* t = C->find_trg(name);
   if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
   if (Nt) *Nt = t->Nt;
-  if (trg_dim) *trg_dim = t->trg_dim;
+  if (trg_dim) *trg_dim = t->n_nrm ? t->trg_dim / 3 : t->trg_dim;  // values per target that eval_direct returns
   return 0;
 }
 
@@ -746,17 +778,26 @@ int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t 
   FMM_ENTER(fmm);
   FmmTrg* t = trg_name ? C->find_trg(trg_name) : nullptr;
   if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
-  if (n != t->Nt * t->trg_dim) return set_error(SCTL_B200_ERR_ARG, "U must hold Nt*TrgDim = %lld values", (long long)(t->Nt * t->trg_dim));
+  const bool dotn = t->n_nrm != 0;
+  if (dotn && t->n_nrm != t->Nt * 3) return set_error(SCTL_B200_ERR_ARG, "target '%s': %lld normal values, expected Nt*3 = %lld", trg_name, (long long)t->n_nrm, (long long)(t->Nt * 3));
+  const int k1out = dotn ? t->trg_dim / 3 : t->trg_dim;
+  if (n != t->Nt * k1out) return set_error(SCTL_B200_ERR_ARG, "U must hold Nt*%d = %lld values", k1out, (long long)(t->Nt * k1out));
   if (n == 0) return 0;
   if (!U) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
   const size_t esz = elem_size(C->dtype);
   const bool dp = flags & SCTL_B200_DEVICE_PTRS;
   cudaStream_t st = c->stream;
-  void* dU = U;
+  void* dU = U;  // where the caller-visible result is produced on the device
   int rc;
   if (!dp) {
     if ((rc = t->U.reserve((size_t)n * esz))) return rc;
     dU = t->U.p;
+  }
+  void* dSum = dU;  // where the kernels accumulate (full TrgDim values per target)
+  const int64_t n_full = t->Nt * t->trg_dim;
+  if (dotn) {
+    if ((rc = t->Ufull.reserve((size_t)n_full * esz))) return rc;
+    dSum = t->Ufull.p;
   }
   bool first = true;
   for (auto& a : C->s2t) {
@@ -767,17 +808,21 @@ int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t 
     if (s->n_den != s->Ns * s->src_dim)  // the reference asserts F.Dim() == Ns*SrcDim (fmm-wrapper.txx:533)
       return set_error(SCTL_B200_ERR_ARG, "source '%s': density has %lld values, expected Ns*SrcDim = %lld", a.first.first.c_str(),
                        (long long)s->n_den, (long long)(s->Ns * s->src_dim));
+    if (s->n_wts && s->n_wts != s->Ns)
+      return set_error(SCTL_B200_ERR_ARG, "source '%s': %lld weights, expected Ns = %lld", a.first.first.c_str(), (long long)s->n_wts, (long long)s->Ns);
     if (s->Ns == 0) continue;
     const EvalEntry& E = (C->dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[d->kernel_id];
     if (d->packed_version != s->version) {
       if ((rc = d->rec.reserve((size_t)padded_sources(s->Ns) * E.rec_len * esz))) return rc;
-      if ((rc = pack_device(d->kernel_id, C->dtype, s->Ns, s->X.p, s->normal_dim ? s->Xn.p : nullptr, s->F.p, d->rec.p, st))) return rc;
+      if ((rc = pack_device(d->kernel_id, C->dtype, s->Ns, s->X.p, s->normal_dim ? s->Xn.p : nullptr, s->F.p, s->n_wts ? s->W.p : nullptr, d->rec.p, st)))
+        return rc;
       d->packed_version = s->version;
     }
-    if ((rc = eval_packed_device(d->kernel_id, C->dtype, t->Nt, s->Ns, t->X.p, d->rec.p, dU, C->digits, !first, st, c->sms, nullptr))) return rc;
+    if ((rc = eval_packed_device(d->kernel_id, C->dtype, t->Nt, s->Ns, t->X.p, d->rec.p, dSum, C->digits, !first, st, c->sms, nullptr))) return rc;
     first = false;
   }
-  if (first) CU_TRY(cudaMemsetAsync(dU, 0, (size_t)n * esz, st));
+  if (first) CU_TRY(cudaMemsetAsync(dSum, 0, (size_t)n_full * esz, st));
+  if (dotn) CU_TRY((C->dtype == SCTL_B200_F64 ? contract_normal_f64 : contract_normal_f32)(dSum, t->Xn.p, dU, t->Nt, k1out, st));
   if (!dp) CU_TRY(cudaMemcpyAsync(U, dU, (size_t)n * esz, cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaStreamSynchronize(st));
   return 0;

@@ -60,12 +60,12 @@ struct EvalParams {
 };
 
 // ---------------------------------------------------------------------------------------------
-// pack: AoS (r_src, n_src, v_src) -> records {x,y,z,payload,0-pad}; tail padded with zero records
+// pack: AoS (r_src, n_src, v_src [* src_wts]) -> records {x,y,z,payload,0-pad}; tail padded with zero records
 // ---------------------------------------------------------------------------------------------
 template <class Ker, class Real>
 __global__ void __launch_bounds__(256) pack_kernel(const Real* __restrict__ r_src, const Real* __restrict__ n_src,
-                                                   const Real* __restrict__ v_src, Real* __restrict__ rec, long long Ns,
-                                                   long long Ns_pad) {
+                                                   const Real* __restrict__ v_src, const Real* __restrict__ src_wts,
+                                                   Real* __restrict__ rec, long long Ns, long long Ns_pad) {
   constexpr int REC = rec_len<Ker, Real>();
   const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= Ns_pad) return;
@@ -81,6 +81,11 @@ __global__ void __launch_bounds__(256) pack_kernel(const Real* __restrict__ r_sr
     for (int i = 0; i < Ker::ND; i++) n[i] = n_src[s * Ker::ND + i];
 #pragma unroll
     for (int i = 0; i < Ker::K0; i++) f[i] = v_src[s * Ker::K0 + i];
+    if (src_wts) {  // F <- F * wts: the far-field quadrature weights of BoundaryIntegralOp::ComputeFarField (boundary_integral.txx:1036-1051)
+      const Real w = src_wts[s];
+#pragma unroll
+      for (int i = 0; i < Ker::K0; i++) f[i] *= w;
+    }
     Ker::pack(out + 3, n, f);
   }
   using V = typename VecOf<Real>::type;
@@ -287,6 +292,22 @@ __global__ void __launch_bounds__(256) reduce_kernel(const double* __restrict__ 
     const double prev = accumulate ? (double)v_trg[t * K1 + q] : 0.0;
     v_trg[t * K1 + q] = (Real)(prev + sum[q] * scale);
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// U[t*K1out+k] = sum_l Ufull[(t*K1out+k)*3+l] * n_trg[t*3+l]: the target-normal dot product that
+// BoundaryIntegralOp::ComputeFarField applies after fmm.Eval (boundary_integral.txx:1060-1071). O(Nt).
+// ---------------------------------------------------------------------------------------------
+template <class Real>
+__global__ void __launch_bounds__(256) contract_normal_kernel(const Real* __restrict__ Ufull, const Real* __restrict__ n_trg, Real* __restrict__ U,
+                                                              long long Nt, int K1out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // index into U: t*K1out + k
+  if (i >= Nt * K1out) return;
+  const long long t = i / K1out;
+  Real a = Ufull[i * 3 + 0] * n_trg[t * 3 + 0];
+  a = fma(Ufull[i * 3 + 1], n_trg[t * 3 + 1], a);
+  a = fma(Ufull[i * 3 + 2], n_trg[t * 3 + 2], a);
+  U[i] = a;
 }
 
 template <class Ker, class Real>

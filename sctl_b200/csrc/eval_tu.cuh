@@ -21,9 +21,11 @@ constexpr int RSMALL = 1;             // small-Nt variant
 constexpr bool IS_F32 = sizeof(Real) == 4;
 
 template <class Ker>
-cudaError_t pack_t(const void* r_src, const void* n_src, const void* v_src, void* rec, long long Ns, long long Ns_pad, cudaStream_t st) {
+cudaError_t pack_t(const void* r_src, const void* n_src, const void* v_src, const void* src_wts, void* rec, long long Ns, long long Ns_pad,
+                   cudaStream_t st) {
   const unsigned blocks = (unsigned)((Ns_pad + 255) / 256);
-  pack_kernel<Ker, Real><<<blocks, 256, 0, st>>>((const Real*)r_src, (const Real*)n_src, (const Real*)v_src, (Real*)rec, Ns, Ns_pad);
+  pack_kernel<Ker, Real><<<blocks, 256, 0, st>>>((const Real*)r_src, (const Real*)n_src, (const Real*)v_src, (const Real*)src_wts, (Real*)rec, Ns,
+                                                 Ns_pad);
   count_launch();
   return cudaGetLastError();
 }
@@ -146,6 +148,14 @@ EvalEntry make_entry() {
 }
 
 }  // namespace
+
+cudaError_t SCTL_B200_CONTRACT_FN(const void* Ufull, const void* n_trg, void* U, long long Nt, int K1out, cudaStream_t st) {
+  const long long n = Nt * K1out;
+  if (n == 0) return cudaSuccess;
+  contract_normal_kernel<Real><<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const Real*)Ufull, (const Real*)n_trg, (Real*)U, Nt, K1out);
+  count_launch();
+  return cudaGetLastError();
+}
 
 const EvalEntry* SCTL_B200_TABLE_FN() {
   static const EvalEntry table[NUM_KERNELS] = {

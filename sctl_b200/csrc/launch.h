@@ -15,7 +15,8 @@ struct EvalEntry {
   int rec_len;  // Reals per packed source record
   int k0, k1, nd;
   int R[NUM_RVAR];
-  cudaError_t (*pack)(const void* r_src, const void* n_src, const void* v_src, void* rec, long long Ns, long long Ns_pad, cudaStream_t st);
+  cudaError_t (*pack)(const void* r_src, const void* n_src, const void* v_src, const void* src_wts, void* rec, long long Ns, long long Ns_pad,
+                      cudaStream_t st);
   // launches grid (n_ttiles, p.n_chunks)
   cudaError_t (*eval[NUM_RVAR][NUM_NEWTON])(const EvalParams& p, long long n_ttiles, cudaStream_t st);
   // resident CTAs per SM for that instantiation (queried once)
@@ -33,6 +34,10 @@ const EvalEntry* eval_table_f64();  // [NUM_KERNELS]
 const EvalEntry* eval_table_f32();
 
 void count_launch(int n = 1);
+
+// eval_f64.cu / eval_f32.cu: U = Ufull contracted with the target normals (see contract_normal_kernel)
+cudaError_t contract_normal_f64(const void* Ufull, const void* n_trg, void* U, long long Nt, int K1out, cudaStream_t st);
+cudaError_t contract_normal_f32(const void* Ufull, const void* n_trg, void* U, long long Nt, int K1out, cudaStream_t st);
 
 // peak.cu
 cudaError_t run_peak_f64(double seconds, double* tflops, cudaStream_t st);

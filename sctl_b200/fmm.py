@@ -112,6 +112,19 @@ class ParticleFMM:
             raise ValueError("coordinate arrays must hold 3 values per point")
         capi.check(capi.lib().sctl_b200_fmm_set_trg_coord(self._h, name.encode(), n // 3, p, fl))
 
+    # -- fused glue of BoundaryIntegralOp::ComputeFarField (extensions; not methods of the reference's ParticleFMM) ---------
+    def SetSrcWeights(self, name: str, wts) -> None:
+        """far-field quadrature weights: density * wts[s] is applied on the device when records are packed
+        (the reference scales F_far on the host before SetSrcDensity, boundary_integral.txx:1036-1051). None removes them."""
+        p, n, fl, _k = self._arg(wts)
+        capi.check(capi.lib().sctl_b200_fmm_set_src_weights(self._h, name.encode(), n, p, fl))
+
+    def SetTrgNormal(self, name: str, trg_normal) -> None:
+        """Eval then returns the potential's component triplets dotted with the target normal, TrgDim/3 values per target
+        (trg_normal_dot_prod_ branch, boundary_integral.txx:1060-1071). None removes them."""
+        p, n, fl, _k = self._arg(trg_normal)
+        capi.check(capi.lib().sctl_b200_fmm_set_trg_normal(self._h, name.encode(), n, p, fl))
+
     # -- evaluation (fmm-wrapper.txx:481-562) --------------------------------------------------------------------
     def EvalDirect(self, trg_name: str, U=None):
         """U (overwritten; created when None or wrongly sized — fmm-wrapper.txx:500-502) = sum over all sources with an S2T

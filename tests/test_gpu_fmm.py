@@ -95,3 +95,32 @@ def test_registry_errors():
     fmm.AddTrg("T2", sl, sl)
     fmm.SetTrgCoord("T2", np.zeros(30))
     assert np.all(fmm.Eval("T2") == 0)
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+def test_far_field_glue_weights_and_target_normal(checker, dt):
+    """the host-side glue of BoundaryIntegralOp::ComputeFarField fused on the device: F_far *= wts_far (boundary_integral.txx:1036-1051)
+    and the target-normal dot product after Eval (:1060-1071), here with Laplace3D_FxdU (TrgDim 3 -> 1 value per target)"""
+    from sctl_b200 import Laplace3D_FxdU
+
+    N, Ns = 3000, 4100
+    ker = Laplace3D_FxdU()
+    fmm = ParticleFMM(dt)
+    fmm.AddSrc("Src", ker, ker)
+    fmm.AddTrg("Trg", ker, ker)
+    fmm.SetKernelS2T("Src", "Trg", ker)
+    Xt, Xs = synth.uniform(1, 0, 3 * N, dtype=dt), synth.uniform(2, 0, 3 * Ns, dtype=dt)
+    F, W, Nt = synth.uniform(4, 0, Ns, dtype=dt), synth.uniform(5, 0, Ns, dtype=dt) + dt(1), synth.uniform(7, 0, 3 * N, dtype=dt)
+    fmm.SetTrgCoord("Trg", Xt)
+    fmm.SetSrcCoord("Src", Xs)
+    fmm.SetSrcDensity("Src", F)
+    fmm.SetSrcWeights("Src", W)
+    fmm.SetTrgNormal("Trg", Nt)
+    U = fmm.Eval("Trg")
+    full = checker.eval(2, Xt, Xs, None, (F * W).astype(dt)).astype(np.float64).reshape(N, 3)
+    want = (full * Nt.astype(np.float64).reshape(N, 3)).sum(1)
+    assert U.shape == (N,) and rel_l2(U, want) <= 20 * TOL[np.dtype(dt)]  # the dot product can cancel: looser than the per-component bound
+    # removing both restores the plain result
+    fmm.SetSrcWeights("Src", None)
+    fmm.SetTrgNormal("Trg", None)
+    assert rel_l2(fmm.Eval("Trg"), checker.eval(2, Xt, Xs, None, F)) <= TOL[np.dtype(dt)]

@@ -167,6 +167,28 @@ int main(int argc, char** argv) {
     const auto Ucf = run_particle_fmm<float, CpuCopy>(3000, 2);
     report("sctl_b200::ParticleFMM<float,3> registry, 2 density updates", rel_l2(Ugf, Ucf), 1e-5);
   }
+  {  // KernelMatrix from inside an OpenMP parallel region, as BoundaryIntegralOp::SetupNear calls it (boundary_integral.txx:949-986)
+    using Gpu = sctl::Stokes3D_DxU;
+    using Cpu = sctl::GenericKernel<CpuCopy<sctl::kernel_impl::Stokes3D_DxU>>;
+    const Long nb = 32, nt = 41, ns = 29;
+    sctl::Vector<double> Xt(nb * nt * 3), Xs(nb * ns * 3), Xn(nb * ns * 3);
+    fill(Xt), fill(Xs), fill(Xn);
+    sctl::Vector<double> err(nb);
+    Gpu gpu;
+    Cpu cpu;
+#pragma omp parallel for schedule(dynamic)
+    for (Long b = 0; b < nb; b++) {
+      const sctl::Vector<double> xt(nt * 3, Xt.begin() + b * nt * 3, false), xs(ns * 3, Xs.begin() + b * ns * 3, false), xn(ns * 3, Xn.begin() + b * ns * 3, false);
+      sctl::Matrix<double> M, Mref;
+      gpu.KernelMatrix<double, true>(M, xt, xs, xn);
+      cpu.KernelMatrix<double, false>(Mref, xt, xs, xn);
+      const sctl::Vector<double> a(M.Dim(0) * M.Dim(1), M.begin(), false), c(Mref.Dim(0) * Mref.Dim(1), Mref.begin(), false);
+      err[b] = rel_l2(a, c);
+    }
+    double worst = 0;
+    for (Long b = 0; b < nb; b++) worst = std::max(worst, err[b]);
+    report("KernelMatrix<double,true> from 32 OpenMP iterations (concurrent callers)", worst, 1e-12);
+  }
   std::printf("launches issued by libsctl_b200: %lld\n", (long long)sctl_b200_launch_count());
   std::printf(g_fail ? "SHIM TEST FAILED (%d)\n" : "SHIM TEST PASSED\n", g_fail);
   return g_fail ? 1 : 0;

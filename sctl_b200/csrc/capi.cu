@@ -171,13 +171,18 @@ static EvalPlan make_plan(const EvalEntry& E, int dtype, int64_t Nt, int64_t Ns,
   P.Ns_pad = P.n_tiles * EVAL_TILE;
   P.n_ttiles = (Nt + (long long)EVAL_THREADS * R - 1) / ((long long)EVAL_THREADS * R);
   P.nt_stride = (Nt + 31) / 32 * 32;
-  // split the source range until there are ~64 CTAs per resident slot (tail <= ~1.5 %), keeping at least
-  // 2 tiles (512 sources) per chunk and at most 1 GiB of partial sums
+  // Split the source range into chunks (blockIdx.y): aim at ~64 CTAs per resident slot, at most 1 GiB of partial sums.
+  // Many short CTAs beat few long ones: the block scheduler refills slots as they free up, so short CTAs balance the SMs
+  // dynamically, while a wave-quantised plan leaves SMs idle behind the last wave (measured with scripts/sweep_chunks.py,
+  // profiles/r01o_chunk_sweep.txt: at 20k x 20k 1-3 tiles per chunk run in 0.33-0.35 ms, 4-8 tiles in 0.42-0.56 ms; a
+  // cost model built on whole waves picked the latter). Two tiles per chunk keep the per-CTA prologue below 2 %; one tile
+  // per chunk only when even that leaves fewer than 4 CTAs per slot.
   const int occ = E.occupancy[P.rvar][P.newton]();
   const long long slots = (long long)occ * sms;
   const long long want = (long long)env_int("SCTL_B200_CTAS_PER_SLOT", 64) * slots;
   long long chunks = (want + P.n_ttiles - 1) / P.n_ttiles;
-  const long long max_by_tiles = P.n_tiles / 2 > 0 ? P.n_tiles / 2 : 1;
+  long long max_by_tiles = P.n_tiles / 2 > 0 ? P.n_tiles / 2 : 1;
+  if (max_by_tiles * P.n_ttiles < 4 * slots) max_by_tiles = P.n_tiles;
   const long long max_by_mem = (long long)((1ull << 30) / ((size_t)E.k1 * 8 * (size_t)P.nt_stride));
   if (chunks > max_by_tiles) chunks = max_by_tiles;
   if (chunks > max_by_mem) chunks = max_by_mem;

@@ -179,3 +179,211 @@ class _null:
 
     def __exit__(self, *a):
         return False
+
+
+class ShardedParticleFMM:
+    """ParticleFMM<Real,3> registry + EvalDirect over the ranks of a process group (one process per GPU).
+
+    The reference's EvalDirect with an MPI communicator (fmm-wrapper.txx:490-562): every rank hands in ITS particles; targets
+    are re-partitioned evenly (PartitionN, :504-510), every source block travels round an Isend/Irecv ring on EVERY call
+    (:537-558) and the potentials are sent back to the ranks that own the targets (:560-561). Here:
+
+      * sources (coordinates, normals, densities, weights) are all-gathered over NCCL when they are SET, not when they
+        are evaluated: a solver that sets coordinates once and a new density per iteration (boundary_integral.txx:777-778
+        vs :1054) moves 8*K0 bytes per source per iteration, and every Eval is a purely local launch sequence on the
+        device-resident registry of sctl_b200.fmm.ParticleFMM;
+      * targets stay with their owner when the ranks hold (almost) equal numbers; when they do not (more than `imbalance`
+        above the mean) they are re-partitioned by the reference's formula - all-gather the coordinates, evaluate block
+        [Nt*r/np, Nt*(r+1)/np), all-gather the potentials and keep the owner's rows - so that no GPU waits for another.
+
+    `local` is the per-rank registry (default: the CUDA one); the CPU gloo tests inject an oracle-backed stand-in.
+    """
+
+    def __init__(self, dtype=None, group=None, local=None, device=None, imbalance: float = 0.05):
+        import numpy as np
+
+        self.dtype = np.dtype(dtype or np.float64)
+        self.group = group
+        if local is None:
+            from .fmm import ParticleFMM
+
+            local = ParticleFMM(self.dtype)
+        self.local = local
+        self.device = torch.device(device) if device is not None else (torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu"))
+        self.imbalance = float(imbalance)
+        self._src_counts = {}  # source name -> particles per rank
+        self._src_dims = {}  # source name -> (SrcDim, NormalDim)
+        self._trg = {}  # target name -> dict(counts, moved, lo, hi, dim)
+        self._bufs = {}
+
+    # -- helpers -----------------------------------------------------------------------------------------
+    def _world(self):
+        if not dist.is_available() or not dist.is_initialized():
+            return 0, 1
+        return dist.get_rank(self.group), dist.get_world_size(self.group)
+
+    def _tensor(self, a):
+        if a is None:
+            return None
+        tdt = torch.float64 if self.dtype.itemsize == 8 else torch.float32
+        if not isinstance(a, torch.Tensor):
+            import numpy as np
+
+            a = torch.from_numpy(np.ascontiguousarray(a, dtype=self.dtype).reshape(-1))
+        return a.to(device=self.device, dtype=tdt).contiguous().reshape(-1)
+
+    def _to_local(self, t):
+        """what the per-rank registry accepts: CUDA tensors as they are, CPU tensors as numpy"""
+        if t is None:
+            return None
+        return t if t.is_cuda else t.numpy()
+
+    def _counts(self, n_local):
+        rank, size = self._world()
+        if size == 1:
+            return [n_local]
+        t = torch.tensor([n_local], dtype=torch.int64, device=self.device)
+        out = torch.empty(size, dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(out, t, group=self.group)
+        return [int(v) for v in out.tolist()]
+
+    def _gather(self, local, width, counts):
+        """replica of every rank's block of an AoS array with `width` values per particle (fresh tensor)"""
+        rank, size = self._world()
+        if size == 1:
+            return local
+        if local.numel() != width * counts[rank]:
+            raise ValueError(f"expected {width} values for each of this rank's {counts[rank]} particles, got {local.numel()}")
+        out = torch.empty(width * sum(counts), dtype=local.dtype, device=local.device)
+        if out.numel() == 0:
+            return out
+        if len(set(counts)) == 1:
+            dist.all_gather_into_tensor(out, local, group=self.group)
+        else:
+            off = [0]
+            for c in counts:
+                off.append(off[-1] + width * c)
+            out[off[rank]:off[rank + 1]].copy_(local)
+            for r in range(size):
+                if counts[r]:
+                    dist.broadcast(out[off[r]:off[r + 1]], src=dist.get_global_rank(self.group, r) if self.group is not None else r, group=self.group)
+        return out
+
+    # -- registry: identical on every rank (fmm-wrapper.txx:240-443) ---------------------------------------------
+    def SetAccuracy(self, digits):
+        self.local.SetAccuracy(digits)
+
+    def SetKernels(self, ker_m2m, ker_m2l, ker_l2l):
+        self.local.SetKernels(ker_m2m, ker_m2l, ker_l2l)
+
+    def AddSrc(self, name, ker_s2m, ker_s2l):
+        self.local.AddSrc(name, ker_s2m, ker_s2l)
+        self._src_counts[name] = None
+        self._src_dims[name] = (ker_s2m.SrcDim(), ker_s2m.NormalDim())
+
+    def AddTrg(self, name, ker_m2t, ker_l2t):
+        self.local.AddTrg(name, ker_m2t, ker_l2t)
+        self._trg[name] = dict(counts=None, moved=False, dim=ker_l2t.TrgDim(), out_dim=ker_l2t.TrgDim())
+
+    def SetKernelS2T(self, src_name, trg_name, ker_s2t):
+        self.local.SetKernelS2T(src_name, trg_name, ker_s2t)
+
+    def DeleteSrc(self, name):
+        self.local.DeleteSrc(name)
+        self._src_counts.pop(name, None)
+
+    def DeleteTrg(self, name):
+        self.local.DeleteTrg(name)
+        self._trg.pop(name, None)
+
+    # -- particle data: this rank's particles in, replicas / blocks into the per-rank registry ---------------------
+    def SetSrcCoord(self, name, src_coord, src_normal=None):
+        X, Xn = self._tensor(src_coord), self._tensor(src_normal)
+        if X.numel() % 3:
+            raise ValueError("coordinate arrays must hold 3 values per point")
+        counts = self._counts(X.numel() // 3)
+        self._src_counts[name] = counts
+        nd = self._src_dims[name][1]
+        gX = self._gather(X, 3, counts)
+        gN = self._gather(Xn, nd, counts) if (nd and Xn is not None) else None
+        self.local.SetSrcCoord(name, self._to_local(gX), self._to_local(gN))
+
+    def _src_counts_of(self, name):
+        counts = self._src_counts.get(name)
+        if counts is None:
+            raise ValueError(f"SetSrcCoord('{name}') must come first: it fixes how many sources every rank holds")
+        return counts
+
+    def SetSrcDensity(self, name, src_density):
+        F = self._tensor(src_density)
+        self.local.SetSrcDensity(name, self._to_local(self._gather(F, self._src_dims[name][0], self._src_counts_of(name))))
+
+    def SetSrcWeights(self, name, wts):
+        if wts is None:
+            return self.local.SetSrcWeights(name, None)
+        self.local.SetSrcWeights(name, self._to_local(self._gather(self._tensor(wts), 1, self._src_counts_of(name))))
+
+    def _trg_block(self, name, t, width):
+        """this rank's share of a per-target array: its own rows, or block `rank` of the gathered array when re-partitioned"""
+        T = self._trg[name]
+        if not T["moved"]:
+            return t
+        g = self._gather(t, width, T["counts"])
+        return g[width * T["lo"]:width * T["hi"]].contiguous()
+
+    def SetTrgCoord(self, name, trg_coord):
+        X = self._tensor(trg_coord)
+        if X.numel() % 3:
+            raise ValueError("coordinate arrays must hold 3 values per point")
+        rank, size = self._world()
+        T = self._trg[name]
+        T["counts"] = counts = self._counts(X.numel() // 3)
+        total = sum(counts)
+        T["moved"] = size > 1 and total > 0 and max(counts) > (1.0 + self.imbalance) * total / size + 1
+        T["lo"], T["hi"] = partition(total, rank, size) if T["moved"] else (sum(counts[:rank]), sum(counts[:rank + 1]))
+        self.local.SetTrgCoord(name, self._to_local(self._trg_block(name, X, 3)))
+
+    def SetTrgNormal(self, name, trg_normal):
+        T = self._trg[name]
+        if trg_normal is None:
+            T["out_dim"] = T["dim"]
+            return self.local.SetTrgNormal(name, None)
+        if T["counts"] is None:
+            raise ValueError(f"SetTrgCoord('{name}') must come first")
+        T["out_dim"] = T["dim"] // 3
+        self.local.SetTrgNormal(name, self._to_local(self._trg_block(name, self._tensor(trg_normal), 3)))
+
+    # -- evaluation ----------------------------------------------------------------------------------------------
+    def EvalDirect(self, trg_name, U=None):
+        """potentials of THIS rank's targets from ALL ranks' sources (overwritten; fmm-wrapper.txx:500-502, :560-561)"""
+        rank, size = self._world()
+        T = self._trg[trg_name]
+        if T["counts"] is None:
+            raise ValueError(f"SetTrgCoord('{trg_name}') must come first")
+        k = T["out_dim"]
+        n_own = T["counts"][rank] * k
+        tdt = torch.float64 if self.dtype.itemsize == 8 else torch.float32
+        if not T["moved"]:
+            if U is None or not isinstance(U, torch.Tensor) or U.numel() != n_own or U.device != self.device or U.dtype != tdt:
+                U = torch.zeros(n_own, dtype=tdt, device=self.device)
+            if U.is_cuda:
+                self.local.EvalDirect(trg_name, U)
+            else:
+                U.copy_(torch.from_numpy(self.local.EvalDirect(trg_name)))
+            return U
+        blk = torch.zeros((T["hi"] - T["lo"]) * k, dtype=tdt, device=self.device)
+        if blk.is_cuda:
+            self.local.EvalDirect(trg_name, blk)
+        else:
+            blk.copy_(torch.from_numpy(self.local.EvalDirect(trg_name)))
+        total = sum(T["counts"])
+        g = self._gather(blk, k, [partition(total, r, size)[1] - partition(total, r, size)[0] for r in range(size)])
+        own0 = sum(T["counts"][:rank]) * k
+        out = g[own0:own0 + n_own]
+        if U is not None and isinstance(U, torch.Tensor) and U.numel() == n_own and U.device == self.device and U.dtype == tdt:
+            U.copy_(out)
+            return U
+        return out.clone()
+
+    def Eval(self, trg_name, U=None):
+        return self.EvalDirect(trg_name, U)

@@ -124,3 +124,26 @@ def test_far_field_glue_weights_and_target_normal(checker, dt):
     fmm.SetSrcWeights("Src", None)
     fmm.SetTrgNormal("Trg", None)
     assert rel_l2(fmm.Eval("Trg"), checker.eval(2, Xt, Xs, None, F)) <= TOL[np.dtype(dt)]
+
+
+def test_sharded_registry_single_rank(checker):
+    """ShardedParticleFMM without a process group (one rank): device tensors in, device tensor out, same numbers"""
+    import torch
+
+    from sctl_b200.distributed import ShardedParticleFMM
+
+    N = 3000
+    dt = np.float64
+    sl, dl = Stokes3D_FxU(), Stokes3D_DxU()
+    Xt, Xd, Nd, Fd = (synth.uniform(s, 0, 3 * N, dtype=dt) for s in (1, 2, 3, 4))
+    fmm = ShardedParticleFMM(dt)
+    fmm.SetKernels(sl, sl, sl)
+    fmm.AddTrg("U", sl, sl)
+    fmm.AddSrc("DL", dl, dl)
+    fmm.SetKernelS2T("DL", "U", dl)
+    fmm.SetTrgCoord("U", torch.from_numpy(Xt).cuda())
+    fmm.SetSrcCoord("DL", Xd, Nd)
+    fmm.SetSrcDensity("DL", Fd)
+    U = fmm.Eval("U")
+    assert U.is_cuda and U.numel() == 3 * N
+    assert rel_l2(U.cpu().numpy(), checker.eval(4, Xt, Xd, Nd, Fd)) <= TOL[np.dtype(dt)]

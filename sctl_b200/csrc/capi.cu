@@ -164,10 +164,14 @@ static int env_int(const char* name, int dflt) {
 static EvalPlan make_plan(const EvalEntry& E, int dtype, int64_t Nt, int64_t Ns, int digits, int sms) {
   EvalPlan P{};
   P.newton = newton_level(dtype, digits);
-  // small target sets use the R=1 variant so that fewer lanes idle in the ragged last tile
-  P.rvar = (Nt >= (int64_t)env_int("SCTL_B200_RBIG_MIN_NT", 2048)) ? 1 : 0;
-  const int R = E.R[P.rvar];
+  // The register-blocked variant (R targets per thread) needs enough CTAs to balance 148 SMs; problems that give it fewer
+  // than ~7 CTAs per SM at one tile per chunk (N = M below ~15k), and small target sets (ragged last tile), run the R=1
+  // variant: 128 targets per CTA, 6x the CTAs (profiles/r01q_small_n_rvar.txt: 0.129 vs 0.143 ms at 8k x 8k, 0.065 vs
+  // 0.107 ms at 4k x 4k; the blocked variant wins from 20k x 20k up).
   P.n_tiles = (Ns + EVAL_TILE - 1) / EVAL_TILE;
+  const long long ttiles_big = (Nt + (long long)EVAL_THREADS * E.R[1] - 1) / ((long long)EVAL_THREADS * E.R[1]);
+  P.rvar = (Nt >= (int64_t)env_int("SCTL_B200_RBIG_MIN_NT", 2048) && ttiles_big * P.n_tiles >= (long long)env_int("SCTL_B200_RBIG_MIN_CTAS_PER_SM", 7) * sms) ? 1 : 0;
+  const int R = E.R[P.rvar];
   P.Ns_pad = P.n_tiles * EVAL_TILE;
   P.n_ttiles = (Nt + (long long)EVAL_THREADS * R - 1) / ((long long)EVAL_THREADS * R);
   P.nt_stride = (Nt + 31) / 32 * 32;
@@ -235,6 +239,12 @@ static int eval_packed_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
   return 0;
 }
 
+// Small problems take the one-launch kernel of small_impl.cuh: every thread there walks Ns/8 sources, so it wins while the
+// tiled path cannot fill the SMs (thresholds measured with scripts/latency.py, profiles/r01r_small_path.txt).
+static bool use_small_path(int64_t Nt, int64_t Ns) {
+  return Ns <= (int64_t)env_int("SCTL_B200_SMALL_MAX_NS", 8192) && Nt * Ns <= (int64_t)env_int("SCTL_B200_SMALL_MAX_PAIRS", 25000000);
+}
+
 // pack + eval (+ reduce). ev (optional): 4 events recorded around pack | eval | reduce.
 static int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
                        const void* v_src, void* v_trg, int digits, bool accumulate, cudaStream_t st, int sms, cudaEvent_t* ev) {
@@ -248,6 +258,14 @@ static int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const v
     return 0;
   }
   if (Ns > (int64_t)EVAL_TILE * 0x7fffffffLL) return set_error(SCTL_B200_ERR_ARG, "Ns too large");
+  if (use_small_path(Nt, Ns)) {  // one launch: no record buffer, no partial sums
+    if (ev) CU_TRY(cudaEventRecord(ev[0], st));
+    if (ev) CU_TRY(cudaEventRecord(ev[1], st));
+    CU_TRY(E.small[newton_level(dtype, digits)](r_trg, r_src, n_src, v_src, nullptr, v_trg, Nt, Ns, kernel_scale(kernel_id), accumulate ? 1 : 0, sms, st));
+    if (ev) CU_TRY(cudaEventRecord(ev[2], st));
+    if (ev) CU_TRY(cudaEventRecord(ev[3], st));
+    return 0;
+  }
   DevAlloc rec;
   int rc = rec.alloc((size_t)padded_sources(Ns) * E.rec_len * esz, st);
   if (rc) return rc;

@@ -2,6 +2,7 @@
 // instantiates pack/eval/reduce/kmat for all eight micro-kernels and fills the launch table.
 #include "kmat_impl.cuh"
 #include "launch.h"
+#include "small_impl.cuh"
 
 namespace sctl_b200 {
 namespace {
@@ -55,12 +56,38 @@ cudaError_t eval_t(const EvalParams& p, long long n_ttiles, cudaStream_t st) {
 
 template <class Ker, int R, int NEWTON>
 int occ_t() {
+  static thread_local int cached_dev = -1, cached = 1;  // queried once per host thread and device
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (cached_dev == dev) return cached;
   auto kern = eval_kernel<Ker, Real, R, NEWTON, minb_for<R>()>;
   constexpr size_t smem = eval_smem_bytes<Ker, Real>();
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int n = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, EVAL_THREADS, smem) != cudaSuccess || n < 1) n = 1;
+  cached_dev = dev;
+  cached = n;
   return n;
+}
+
+template <class Ker, int NEWTON, int TPW>
+cudaError_t small_launch(const void* r_trg, const void* r_src, const void* n_src, const void* v_src, const void* src_wts, void* v_trg, long long Nt,
+                         long long Ns, double scale, int accumulate, cudaStream_t st) {
+  const long long blocks = (Nt + TPW - 1) / TPW;
+  if (blocks > 0x7fffffffLL) return cudaErrorInvalidValue;
+  eval_small_kernel<Ker, Real, NEWTON, TPW><<<(unsigned)blocks, SMALL_THREADS, 0, st>>>((const Real*)r_trg, (const Real*)r_src, (const Real*)n_src,
+                                                                                     (const Real*)v_src, (const Real*)src_wts, (Real*)v_trg, Nt,
+                                                                                     Ns, scale, accumulate);
+  count_launch();
+  return cudaGetLastError();
+}
+// targets per CTA: as many as still give every SM about one CTA
+template <class Ker, int NEWTON>
+cudaError_t small_t(const void* r_trg, const void* r_src, const void* n_src, const void* v_src, const void* src_wts, void* v_trg, long long Nt,
+                    long long Ns, double scale, int accumulate, int sms, cudaStream_t st) {
+  if (Nt >= 32ll * sms) return small_launch<Ker, NEWTON, 32>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
+  if (Nt >= 16ll * sms) return small_launch<Ker, NEWTON, 16>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
+  return small_launch<Ker, NEWTON, 8>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
 }
 
 template <class Ker>
@@ -136,6 +163,9 @@ EvalEntry make_entry() {
   e.occupancy[1][0] = occ_t<Ker, rbig_for<Ker>(), 0>;
   e.occupancy[1][1] = occ_t<Ker, rbig_for<Ker>(), 1>;
   e.occupancy[1][2] = occ_t<Ker, rbig_for<Ker>(), IS_F32 ? 1 : 2>;
+  e.small[0] = small_t<Ker, 0>;
+  e.small[1] = small_t<Ker, 1>;
+  e.small[2] = small_t<Ker, IS_F32 ? 1 : 2>;
   e.kmat[0] = kmat_t<Ker, 0>;
   e.kmat[1] = kmat_t<Ker, 1>;
   e.kmat[2] = kmat_t<Ker, IS_F32 ? 1 : 2>;

@@ -23,6 +23,9 @@ struct EvalEntry {
   int (*occupancy[NUM_RVAR][NUM_NEWTON])();
   cudaError_t (*reduce)(const double* partial, void* v_trg, long long Nt, long long nt_stride, int n_chunks, double scale, int accumulate,
                         cudaStream_t st);
+  // one-launch path for small problems straight from the AoS arrays (small_impl.cuh)
+  cudaError_t (*small[NUM_NEWTON])(const void* r_trg, const void* r_src, const void* n_src, const void* v_src, const void* src_wts, void* v_trg,
+                                   long long Nt, long long Ns, double scale, int accumulate, int sms, cudaStream_t st);
   cudaError_t (*kmat[NUM_NEWTON])(const void* r_trg, const void* r_src, const void* n_src, void* M, long long Nt, long long Ns, double scale,
                                   cudaStream_t st);
   // batched small-block KernelMatrix; [1] = with the target-normal contraction (null when TrgDim is not a multiple of 3)

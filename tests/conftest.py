@@ -35,3 +35,22 @@ def reference():
     if r is None:
         pytest.skip("oracle/_ref not built (needs /root/reference)")
     return r
+
+
+# Modules whose Eval tests must hold on BOTH device paths: the tiled pack -> eval -> reduce path and the one-launch
+# small-problem kernel (sctl_b200/csrc/small_impl.cuh). The library picks by problem size; the tests pin each in turn.
+_BOTH_PATHS = {"test_gpu_parity", "test_gpu_edge_cases", "test_gpu_canary", "test_gpu_threads"}
+
+
+def pytest_generate_tests(metafunc):
+    if metafunc.module.__name__.split(".")[-1] in _BOTH_PATHS and "eval_path" in metafunc.fixturenames:
+        metafunc.parametrize("eval_path", ["tiled", "small"], indirect=True)
+
+
+@pytest.fixture
+def eval_path(request, monkeypatch):
+    if request.param == "tiled":
+        monkeypatch.setenv("SCTL_B200_SMALL_MAX_PAIRS", "0")
+    else:  # force the small kernel wherever its size guard allows it (Ns <= 8192)
+        monkeypatch.setenv("SCTL_B200_SMALL_MAX_PAIRS", str(2**31 - 1))
+    return request.param

@@ -7,7 +7,7 @@ import pytest
 
 from sctl_b200 import KERNELS, capi, synth
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("eval_path")]
 GUARD = 4096
 
 

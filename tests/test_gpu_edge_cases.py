@@ -8,7 +8,7 @@ import pytest
 from sctl_b200 import KERNELS, capi, synth
 from util import TOL, rel_l2
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("eval_path")]
 
 
 @pytest.mark.parametrize("kid", [0, 3, 4])

@@ -6,7 +6,7 @@ import pytest
 from sctl_b200 import KERNELS, capi, synth
 from util import TOL, rel_l2
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("eval_path")]
 
 DTYPES = [np.float64, np.float32]
 
@@ -17,7 +17,7 @@ def _problem(kid, Nt, Ns, dt, seed=0, coincident=64):
 
 @pytest.mark.parametrize("dt", DTYPES)
 @pytest.mark.parametrize("kid", range(8))
-@pytest.mark.parametrize("Nt,Ns", [(1, 1), (7, 300), (300, 7), (1000, 1003), (2051, 5000), (4099, 2500)])
+@pytest.mark.parametrize("Nt,Ns", [(1, 1), (7, 300), (300, 7), (1000, 1003), (2051, 5000), (4099, 2500), (5003, 700)])
 def test_eval_matches_checker(checker, kid, dt, Nt, Ns):
     Xt, Xs, Xn, F = _problem(kid, Nt, Ns, dt)
     want = checker.eval(kid, Xt, Xs, Xn, F)
@@ -108,7 +108,7 @@ def test_launch_counter_moves():
     n0 = capi.launch_count()
     Xt, Xs, Xn, F = _problem(0, 10, 10, np.float64)
     KERNELS[0]().Eval(None, Xt, Xs, Xn, F)
-    assert capi.launch_count() >= n0 + 2
+    assert capi.launch_count() >= n0 + 1  # the small path is ONE launch, the tiled path two or three
 
 
 @pytest.mark.parametrize("kid,dt", [(3, np.float64), (1, np.float32)])

@@ -9,7 +9,7 @@ import pytest
 from sctl_b200 import KERNELS, capi, synth
 from util import rel_l2
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("eval_path")]
 
 
 def test_concurrent_eval_and_kernel_matrix_from_host_threads():

@@ -33,3 +33,20 @@ for n in (64, 256, 1000, 2000, 4000, 8000, 16000):
     torch.cuda.synchronize()
     w2 = time.perf_counter()
     print(f"{d['name']} {np.dtype(dt).name} N=M={n:6d}: host enqueue {1e6 * (w1 - w0) / reps:7.1f} us/call, device {1e3 * e0.elapsed_time(e1) / reps:7.1f} us/call, pairs/s {n * n / (e0.elapsed_time(e1) / reps) * 1e3:.3e}")
+
+# host-pointer entry (what the C++ header shim calls): pageable numpy buffers in, result out, synchronous
+print("host-pointer entry sctl_b200_eval (pageable buffers, synchronous):")
+for n in (64, 256, 1000, 4000, 16000):
+    Xt, Xs, Xn, F = synth.make_problem(d, n, n, dt)
+    U = np.zeros(n * d["trg_dim"], dtype=dt)
+    hp = lambda a: None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+    args = (kid, capi.F64 if dt == np.float64 else capi.F32, n, n, hp(Xt), hp(Xs), hp(Xn) if d["normal_dim"] else None, hp(F), hp(U), -1, capi.OVERWRITE)
+    for _ in range(10):
+        capi.check(L.sctl_b200_eval(*args))
+    reps = 200
+    w0 = time.perf_counter()
+    for _ in range(reps):
+        L.sctl_b200_eval(*args)
+    w1 = time.perf_counter()
+    tm = capi.last_timing()
+    print(f"{d['name']} {np.dtype(dt).name} N=M={n:6d}: wall {1e6 * (w1 - w0) / reps:8.1f} us/call   last call split (ms): {tm}")

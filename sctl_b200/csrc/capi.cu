@@ -77,7 +77,12 @@ struct DevCtx {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   int sms = 0;
+  // staging pair for small host-pointer calls (allocated on first use, kept for the thread's lifetime): pinned host
+  // block + device block, so that a call is ONE H2D copy, the kernels, ONE D2H copy and one synchronisation
+  void* h_stage = nullptr;
+  void* d_stage = nullptr;
 };
+constexpr size_t STAGE_BYTES = 1u << 20;
 static thread_local std::vector<DevCtx> t_ctx;
 static std::mutex g_pool_mutex;
 static std::vector<int> g_pool_configured;
@@ -305,6 +310,42 @@ static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
   return ms;
 }
 
+// Small host-pointer calls (all arrays together below STAGE_BYTES): the five pageable copies, five stream-ordered
+// allocations and six event records of the general path cost more than the sum itself (72 us wall at 64 x 64,
+// profiles/r01r_small_path.txt), so the arrays are gathered in a pinned block and cross the bus in one copy each way.
+static int eval_host_staged(DevCtx* c, int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                            const void* v_src, void* v_trg, int digits, bool accumulate, const size_t (&bytes)[5], const size_t (&off)[6]) {
+  cudaStream_t st = c->stream;
+  if (!c->h_stage) {
+    CU_TRY(cudaMallocHost(&c->h_stage, STAGE_BYTES));
+    cudaError_t e = cudaMalloc(&c->d_stage, STAGE_BYTES);
+    if (e != cudaSuccess) {
+      cudaFreeHost(c->h_stage);
+      c->h_stage = nullptr;
+      cudaGetLastError();
+      return set_error(SCTL_B200_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", STAGE_BYTES, cudaGetErrorString(e));
+    }
+  }
+  char* h = (char*)c->h_stage;
+  char* d = (char*)c->d_stage;
+  const void* in[5] = {r_trg, r_src, n_src, v_src, accumulate ? v_trg : nullptr};
+  for (int i = 0; i < 5; i++)
+    if (in[i] && bytes[i]) memcpy(h + off[i], in[i], bytes[i]);
+  const size_t in_bytes = accumulate ? off[5] : off[4];
+  cudaEvent_t* ev = c->ev;
+  CU_TRY(cudaEventRecord(ev[4], st));
+  CU_TRY(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, st));
+  int rc = eval_device(kernel_id, dtype, Nt, Ns, d + off[0], d + off[1], d + off[2], d + off[3], d + off[4], digits, accumulate, st, c->sms, nullptr);
+  if (rc) return rc;
+  CU_TRY(cudaMemcpyAsync(h + off[4], d + off[4], bytes[4], cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaEventRecord(ev[5], st));
+  CU_TRY(cudaStreamSynchronize(st));
+  memcpy(v_trg, h + off[4], bytes[4]);
+  t_timing[0] = t_timing[1] = t_timing[3] = t_timing[4] = 0;
+  t_timing[2] = ev_ms(ev[4], ev[5]);  // copies included: the stages are not timed separately on this path
+  return 0;
+}
+
 static int eval_host_one_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
                                 const void* v_src, void* v_trg, int digits, bool accumulate) {
   DevCtx* c = nullptr;
@@ -314,6 +355,14 @@ static int eval_host_one_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns
   const size_t esz = elem_size(dtype);
   cudaStream_t st = c->stream;
   if (Nt == 0) return 0;
+  {
+    const size_t bytes[5] = {(size_t)Nt * 3 * esz, (size_t)Ns * 3 * esz, (size_t)Ns * ki.normal_dim * esz, (size_t)Ns * ki.src_dim * esz,
+                             (size_t)Nt * ki.trg_dim * esz};
+    size_t off[6] = {0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < 5; i++) off[i + 1] = off[i] + (bytes[i] + 255) / 256 * 256;
+    if (off[5] <= STAGE_BYTES && (size_t)env_int("SCTL_B200_STAGE_MAX_BYTES", (int)STAGE_BYTES) >= off[5])
+      return eval_host_staged(c, kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, v_src, v_trg, digits, accumulate, bytes, off);
+  }
   DevAlloc d_rt, d_rs, d_ns, d_vs, d_vt;
   const size_t b_rt = (size_t)Nt * 3 * esz, b_rs = (size_t)Ns * 3 * esz, b_ns = (size_t)Ns * ki.normal_dim * esz,
                b_vs = (size_t)Ns * ki.src_dim * esz, b_vt = (size_t)Nt * ki.trg_dim * esz;

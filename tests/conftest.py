@@ -51,6 +51,7 @@ def pytest_generate_tests(metafunc):
 def eval_path(request, monkeypatch):
     if request.param == "tiled":
         monkeypatch.setenv("SCTL_B200_SMALL_MAX_PAIRS", "0")
+        monkeypatch.setenv("SCTL_B200_STAGE_MAX_BYTES", "0")  # and the general host-pointer path (per-array copies)
     else:  # force the small kernel wherever its size guard allows it (Ns <= 8192)
         monkeypatch.setenv("SCTL_B200_SMALL_MAX_PAIRS", str(2**31 - 1))
     return request.param

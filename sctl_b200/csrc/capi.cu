@@ -884,6 +884,12 @@ int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t 
       return set_error(SCTL_B200_ERR_ARG, "source '%s': %lld weights, expected Ns = %lld", a.first.first.c_str(), (long long)s->n_wts, (long long)s->Ns);
     if (s->Ns == 0) continue;
     const EvalEntry& E = (C->dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[d->kernel_id];
+    if (use_small_path(t->Nt, s->Ns)) {  // one launch straight from the resident AoS arrays; weights fused, no records needed
+      CU_TRY(E.small[newton_level(C->dtype, C->digits)](t->X.p, s->X.p, s->normal_dim ? s->Xn.p : nullptr, s->F.p, s->n_wts ? s->W.p : nullptr, dSum, t->Nt,
+                                                        s->Ns, kernel_scale(d->kernel_id), first ? 0 : 1, c->sms, st));
+      first = false;
+      continue;
+    }
     if (d->packed_version != s->version) {
       if ((rc = d->rec.reserve((size_t)padded_sources(s->Ns) * E.rec_len * esz))) return rc;
       if ((rc = pack_device(d->kernel_id, C->dtype, s->Ns, s->X.p, s->normal_dim ? s->Xn.p : nullptr, s->F.p, s->n_wts ? s->W.p : nullptr, d->rec.p, st)))

@@ -39,7 +39,7 @@ def reference():
 
 # Modules whose Eval tests must hold on BOTH device paths: the tiled pack -> eval -> reduce path and the one-launch
 # small-problem kernel (sctl_b200/csrc/small_impl.cuh). The library picks by problem size; the tests pin each in turn.
-_BOTH_PATHS = {"test_gpu_parity", "test_gpu_edge_cases", "test_gpu_canary", "test_gpu_threads"}
+_BOTH_PATHS = {"test_gpu_parity", "test_gpu_edge_cases", "test_gpu_canary", "test_gpu_threads", "test_gpu_fmm"}
 
 
 def pytest_generate_tests(metafunc):

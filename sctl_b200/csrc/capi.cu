@@ -64,7 +64,7 @@ static double kernel_scale(int kid) {
 static int newton_level(int dtype, int digits) {
   if (dtype == SCTL_B200_F64) {
     if (digits < 0 || digits > 12) return 2;
-    return digits > 6 ? 1 : 0;
+    return digits > 5 ? 1 : 0;  // the bare MUFU.RSQ64H seed is good to ~2^-19 (5.7 digits)
   }
   return (digits < 0 || digits > 6) ? 1 : 0;
 }

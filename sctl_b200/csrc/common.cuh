@@ -87,19 +87,31 @@ __device__ __forceinline__ double rsqrt_masked(double r2) {
 // ---------------------------------------------------------------------------------------------
 // `lo_any` supplies the (irrelevant) low word of the seed: pass a value whose 64-bit register dies at this point
 // (the partial sum dx^2 + dy^2), so that the seed can be built in that register pair without a move.
-__device__ __forceinline__ double rsqrt_unmasked_full(double r2, double lo_any) {
+// NEWTON = 2: cubic step (full f64 precision). NEWTON = 1: one Newton step written so that the halving costs no
+// integer instruction (e' = 1/2 - (r2 y0)(y0/2) as one DFMA on -y0/2; 4 FP64 instructions instead of 5, ~2^-38).
+// NEWTON = 0: the seed itself (~2^-19 with the undefined low word), 0 extra instructions.
+template <int NEWTON>
+__device__ __forceinline__ double rsqrt_unmasked(double r2, double lo_any) {
   double seed;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(seed) : "d"(r2));
   const double y0 = __hiloint2double(__double2hiint(seed), __double2loint(lo_any));
+  if (NEWTON == 0) return y0;
   const double t = r2 * y0;
+  if (NEWTON == 1) {
+    const double yh = -0.5 * y0;
+    const double e = fma(t, yh, 0.5);
+    return fma(y0, e, y0);
+  }
   const double e = fma(-t, y0, 1.0);
   const double p = fma(e, 0.375, 0.5);
   const double q = e * p;
   return fma(y0, q, y0);
 }
-__device__ __forceinline__ float rsqrt_unmasked_full(float r2, float) {
+template <int NEWTON>
+__device__ __forceinline__ float rsqrt_unmasked(float r2, float) {
   float y0;
   asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y0) : "f"(r2));
+  if (NEWTON == 0) return y0;
   const float t = r2 * y0;
   const float e = fmaf(-t, y0, 1.0f);
   const float h = 0.5f * y0;

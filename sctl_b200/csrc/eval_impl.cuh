@@ -19,7 +19,7 @@
 //   * every tile is summed into per-tile accumulators that are flushed into f64 running sums after the tile
 //     (FP32: 16M-source sums stay inside 1e-5, the reference accumulates in plain f32; FP64: blocked
 //     summation, slightly more accurate than the reference's single in-order accumulator).
-//   * the full-precision instantiations carry NO r2 == 0 test in the hot loop: a coincident pair turns the
+//   * there is NO r2 == 0 test in the hot loop (at any rsqrt refinement level): a coincident pair turns the
 //     tile's partial sums non-finite, which is detected once per tile and repaired by re-running that tile
 //     with the masked rsqrt (exactly-zero contribution, kernel_functions.hpp:28).
 #pragma once
@@ -152,9 +152,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
     for (int k = 0; k < NACC; k++) acc[r][k] = 0.0;
   }
 
-  // Full-precision instantiations run the tile UNMASKED (no r2 == 0 test in the hot loop) and repair the
-  // rare tile that held a coincident pair; the relaxed-digits instantiations keep the masked seed.
-  constexpr bool FAST = (NEWTON == (sizeof(Real) == 8 ? 2 : 1));
+  // Every tile runs UNMASKED (no r2 == 0 test in the hot loop); the rare tile that held a coincident pair is repaired below.
+  constexpr bool FAST = true;
 
   for (int k = 0; k < ntile; k++) {
     const int stage = k % EVAL_STAGES;
@@ -181,7 +180,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
         Real r2p = dx * dx;
         r2p = fma(dy, dy, r2p);
         const Real r2 = fma(dz, dz, r2p);
-        const Real rinv = FAST ? rsqrt_unmasked_full(r2, r2p) : rsqrt_masked<NEWTON>(r2);
+        const Real rinv = rsqrt_unmasked<NEWTON>(r2, r2p);
         Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
       }
     }

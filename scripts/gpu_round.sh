@@ -19,3 +19,16 @@ python bench.py --steps 1 --warmup 3 --no-cpu-baseline > $OUT/bench_short.json 2
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv \
     python bench.py --steps 1 --warmup 3 --no-cpu-baseline > $OUT/ncu_launches.log 2>&1
 tail -2 $OUT/ncu_launches.log
+# DRAM traffic of ONE eval_kernel launch at the bench size (4M x 4M): a metrics-only pass (few replays of a 21 s kernel)
+python scripts/prof_eval.py 3 f64 4000000 1 > $OUT/prof_4m_plain.log 2>&1 && \
+ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:eval_kernel -c 1 --csv \
+    --log-file $OUT/traffic_4m.csv python scripts/prof_eval.py 3 f64 4000000 1 > $OUT/ncu_traffic.log 2>&1
+tail -4 $OUT/traffic_4m.csv
+# the one-launch small kernel and the FP32 kernel, for the record
+python scripts/prof_eval.py 3 f64 2000 3 > /dev/null 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:eval_small_kernel -c 1 -o $OUT/prof_small_stokes_fxu_f64_n2000 \
+    python scripts/prof_eval.py 3 f64 2000 3 > $OUT/ncu_small.log 2>&1
+python scripts/prof_eval.py 3 f32 262144 2 > /dev/null 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:eval_kernel -c 1 -o $OUT/prof_stokes_fxu_f32 \
+    python scripts/prof_eval.py 3 f32 262144 2 > $OUT/ncu_f32.log 2>&1
+ls -la $OUT

@@ -126,6 +126,21 @@ static int get_ctx(DevCtx** out) {
   return 0;
 }
 
+// Releases the calling thread's streams, events and staging blocks. Long-lived caller threads (the main thread, an OpenMP
+// team) keep theirs for the life of the process; the short-lived workers of eval_host_all_gpus call this before they exit.
+static void release_thread_ctx() {
+  for (auto& c : t_ctx) {
+    if (cudaSetDevice(c.dev) != cudaSuccess) continue;
+    if (c.stream) cudaStreamDestroy(c.stream);
+    for (auto& ev : c.ev)
+      if (ev) cudaEventDestroy(ev);
+    if (c.h_stage) cudaFreeHost(c.h_stage);
+    if (c.d_stage) cudaFree(c.d_stage);
+  }
+  t_ctx.clear();
+  cudaGetLastError();
+}
+
 static size_t elem_size(int dtype) { return dtype == SCTL_B200_F64 ? 8 : 4; }
 
 static int check_common(int kernel_id, int dtype, int64_t Nt, int64_t Ns) {
@@ -418,6 +433,7 @@ static int eval_host_all_gpus(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
       rcs[g] = eval_host_one_device(kernel_id, dtype, t1 - t0, Ns, (const char*)r_trg + (size_t)t0 * 3 * esz, r_src, n_src, v_src,
                                     (char*)v_trg + (size_t)t0 * ki.trg_dim * esz, digits, accumulate);
       if (rcs[g]) msgs[g] = t_last_error;
+      release_thread_ctx();
     });
   }
   for (auto& t : th) t.join();

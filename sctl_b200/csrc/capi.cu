@@ -262,7 +262,7 @@ static int eval_packed_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
 // Small problems take the one-launch kernel of small_impl.cuh: every thread there walks Ns/8 sources, so it wins while the
 // tiled path cannot fill the SMs (thresholds measured with scripts/latency.py, profiles/r01r_small_path.txt).
 static bool use_small_path(int64_t Nt, int64_t Ns) {
-  return Ns <= (int64_t)env_int("SCTL_B200_SMALL_MAX_NS", 8192) && Nt * Ns <= (int64_t)env_int("SCTL_B200_SMALL_MAX_PAIRS", 25000000);
+  return Ns <= (int64_t)env_int("SCTL_B200_SMALL_MAX_NS", 8192) && Nt * Ns <= (int64_t)env_int("SCTL_B200_SMALL_MAX_PAIRS", 50000000);
 }
 
 // pack + eval (+ reduce). ev (optional): 4 events recorded around pack | eval | reduce.

@@ -1,5 +1,7 @@
 // Included by eval_f64.cu / eval_f32.cu with SCTL_B200_REAL and SCTL_B200_TABLE_FN defined:
 // instantiates pack/eval/reduce/kmat for all eight micro-kernels and fills the launch table.
+#include <cstdlib>
+
 #include "kmat_impl.cuh"
 #include "launch.h"
 #include "small_impl.cuh"
@@ -81,12 +83,18 @@ cudaError_t small_launch(const void* r_trg, const void* r_src, const void* n_src
   count_launch();
   return cudaGetLastError();
 }
-// targets per CTA: as many as still give every SM about one CTA
+// targets per CTA by target count (measured, profiles/r01w_small_tpw_sweep.txt): 8 below ~3.5k targets, 16 below ~14k, else 32
 template <class Ker, int NEWTON>
 cudaError_t small_t(const void* r_trg, const void* r_src, const void* n_src, const void* v_src, const void* src_wts, void* v_trg, long long Nt,
                     long long Ns, double scale, int accumulate, int sms, cudaStream_t st) {
-  if (Nt >= 32ll * sms) return small_launch<Ker, NEWTON, 32>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
-  if (Nt >= 16ll * sms) return small_launch<Ker, NEWTON, 16>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
+  if (const char* e = getenv("SCTL_B200_SMALL_TPW")) {  // tuning override
+    const int tpw = atoi(e);
+    if (tpw == 32) return small_launch<Ker, NEWTON, 32>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
+    if (tpw == 16) return small_launch<Ker, NEWTON, 16>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
+    if (tpw == 8) return small_launch<Ker, NEWTON, 8>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
+  }
+  if (Nt >= 96ll * sms) return small_launch<Ker, NEWTON, 32>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
+  if (Nt >= 24ll * sms) return small_launch<Ker, NEWTON, 16>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
   return small_launch<Ker, NEWTON, 8>(r_trg, r_src, n_src, v_src, src_wts, v_trg, Nt, Ns, scale, accumulate, st);
 }
 

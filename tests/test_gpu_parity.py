@@ -17,7 +17,7 @@ def _problem(kid, Nt, Ns, dt, seed=0, coincident=64):
 
 @pytest.mark.parametrize("dt", DTYPES)
 @pytest.mark.parametrize("kid", range(8))
-@pytest.mark.parametrize("Nt,Ns", [(1, 1), (7, 300), (300, 7), (1000, 1003), (2051, 5000), (4099, 2500), (5003, 700)])
+@pytest.mark.parametrize("Nt,Ns", [(1, 1), (7, 300), (300, 7), (1000, 1003), (2051, 5000), (4099, 2500), (5003, 700), (15001, 300)])
 def test_eval_matches_checker(checker, kid, dt, Nt, Ns):
     Xt, Xs, Xn, F = _problem(kid, Nt, Ns, dt)
     want = checker.eval(kid, Xt, Xs, Xn, F)

@@ -348,6 +348,18 @@ static int eval_host_staged(DevCtx* c, int kernel_id, int dtype, int64_t Nt, int
     if (in[i] && bytes[i]) memcpy(h + off[i], in[i], bytes[i]);
   const size_t in_bytes = accumulate ? off[5] : off[4];
   cudaEvent_t* ev = c->ev;
+  // Tiny calls: ZERO-COPY. The pinned block is mapped into the device address space (UVA), so the one-launch kernel reads
+  // the arrays over the bus itself and writes v_trg straight back into host memory: one launch + one synchronisation instead
+  // of copy + launch + copy (each a separate device operation of 2-3 us).
+  if (off[5] <= (size_t)env_int("SCTL_B200_ZEROCOPY_MAX_BYTES", 32768) && Ns > 0 && use_small_path(Nt, Ns)) {
+    const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
+    CU_TRY(E.small[newton_level(dtype, digits)](h + off[0], h + off[1], h + off[2], h + off[3], nullptr, h + off[4], Nt, Ns, kernel_scale(kernel_id),
+                                                accumulate ? 1 : 0, c->sms, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    memcpy(v_trg, h + off[4], bytes[4]);
+    t_timing[0] = t_timing[1] = t_timing[2] = t_timing[3] = t_timing[4] = 0;  // not timed on the device: no events on this path
+    return 0;
+  }
   CU_TRY(cudaEventRecord(ev[4], st));
   CU_TRY(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, st));
   int rc = eval_device(kernel_id, dtype, Nt, Ns, d + off[0], d + off[1], d + off[2], d + off[3], d + off[4], digits, accumulate, st, c->sms, nullptr);

@@ -530,7 +530,8 @@ static int kmat_batch_impl(int kernel_id, int dtype, int64_t nbatch, const int64
     const long long len = ns * ki.src_dim * nt * k1out;
     if (M_dsp[b] < 0 || M_dsp[b] + len > M_len) return set_error(SCTL_B200_ERR_ARG, "block %lld does not fit in M (offset %lld + %lld > %lld)", (long long)b, (long long)M_dsp[b], len, (long long)M_len);
     h_M[b] = M_dsp[b];
-    const long long ctas = (nt && ns) ? ((nt + KMAT_THREADS - 1) / KMAT_THREADS) * ((ns + KMAT_SB - 1) / KMAT_SB) : 0;
+    const long long ct = E.kmat_cta_targets[dotn];
+    const long long ctas = (nt && ns) ? ((nt + ct - 1) / ct) * ((ns + KMAT_SB - 1) / KMAT_SB) : 0;
     h_cta[b + 1] = h_cta[b] + ctas;
   }
   const long long n_ctas = h_cta[nbatch];

@@ -109,7 +109,8 @@ cudaError_t reduce_t(const double* partial, void* v_trg, long long Nt, long long
 
 template <class Ker, int NEWTON>
 cudaError_t kmat_t(const void* r_trg, const void* r_src, const void* n_src, void* M, long long Nt, long long Ns, double scale, cudaStream_t st) {
-  const long long gx = (Nt + KMAT_THREADS - 1) / KMAT_THREADS;
+  constexpr int CT = kmat_cta_targets<Ker, Real, false>();
+  const long long gx = (Nt + CT - 1) / CT;
   const long long gy = (Ns + KMAT_SB - 1) / KMAT_SB;
   if (gy > 65535) return cudaErrorInvalidValue;  // callers slab the source range
   dim3 grid((unsigned)gx, (unsigned)gy, 1);
@@ -135,13 +136,17 @@ cudaError_t kmat_batch_t(const void* r_trg, const void* r_src, const void* n_src
 }
 template <class Ker, bool HAS> struct KmatDotN {
   static void fill(EvalEntry& e) {
+    e.kmat_cta_targets[1] = kmat_cta_targets<Ker, Real, true>();
     e.kmat_batch[1][0] = kmat_batch_t<Ker, 0, true>;
     e.kmat_batch[1][1] = kmat_batch_t<Ker, 1, true>;
     e.kmat_batch[1][2] = kmat_batch_t<Ker, IS_F32 ? 1 : 2, true>;
   }
 };
 template <class Ker> struct KmatDotN<Ker, false> {
-  static void fill(EvalEntry& e) { e.kmat_batch[1][0] = e.kmat_batch[1][1] = e.kmat_batch[1][2] = nullptr; }
+  static void fill(EvalEntry& e) {
+    e.kmat_cta_targets[1] = 0;
+    e.kmat_batch[1][0] = e.kmat_batch[1][1] = e.kmat_batch[1][2] = nullptr;
+  }
 };
 
 template <class Ker, int ID>
@@ -177,6 +182,7 @@ EvalEntry make_entry() {
   e.kmat[0] = kmat_t<Ker, 0>;
   e.kmat[1] = kmat_t<Ker, 1>;
   e.kmat[2] = kmat_t<Ker, IS_F32 ? 1 : 2>;
+  e.kmat_cta_targets[0] = kmat_cta_targets<Ker, Real, false>();
   e.kmat_batch[0][0] = kmat_batch_t<Ker, 0, false>;
   e.kmat_batch[0][1] = kmat_batch_t<Ker, 1, false>;
   e.kmat_batch[0][2] = kmat_batch_t<Ker, IS_F32 ? 1 : 2, false>;

@@ -21,6 +21,18 @@ constexpr int KMAT_WARPS = 4;
 constexpr int KMAT_THREADS = KMAT_WARPS * 32;
 constexpr int KMAT_SB = 32;  // sources per CTA
 
+// Kernels whose rows hold ONE value per target (Laplace FxU / DxU, and every target-normal contraction of a 3-vector) would
+// write 4- or 8-byte elements per lane: there a lane owns V = 16 B / sizeof(Real) consecutive targets and stores them as one
+// vector (512 B per warp-wide store instead of 128 / 256 B), which also gives V independent pairs per lane.
+template <class Ker, class Real, bool DOTN>
+__host__ __device__ constexpr int kmat_vec() {
+  return ((DOTN ? Ker::K1 / 3 : Ker::K1) == 1) ? (int)(16 / sizeof(Real)) : 1;
+}
+template <class Ker, class Real, bool DOTN>
+__host__ __device__ constexpr int kmat_cta_targets() {  // targets per CTA (blockIdx.x granularity)
+  return KMAT_THREADS * kmat_vec<Ker, Real, DOTN>();
+}
+
 // One CTA's share of one dense block: targets [tile_x*128, +128) x sources [slab_y*32, +32) of an Nt x Ns problem.
 //   DOTN = false: M[(s*K0+k0)*ld + t*K1+k1]   = w_s * scale * K[k0][k1]                  (KernelMatrix, generic-kernel.txx:284;
 //                                                 w_s = src_wts[s] or 1: the row scaling of boundary_integral.txx:990-997)
@@ -37,6 +49,73 @@ __device__ __forceinline__ void kmat_block(const Real* __restrict__ r_trg, const
 
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
+
+  if constexpr (K1OUT == 1) {
+    constexpr int V = kmat_vec<Ker, Real, DOTN>();
+    using Vec = typename VecOf<Real>::type;
+    const long long t0 = (tile_x * KMAT_WARPS + warp) * (32 * V);
+    if (t0 >= Nt) return;
+    const long long tl = t0 + (long long)lane * V;  // first of this lane's V consecutive targets
+    const int nvalid = (int)max(0ll, min((long long)V, Nt - tl));
+    Real xt[V], yt[V], zt[V], nt[V][3];
+#pragma unroll
+    for (int j = 0; j < V; j++) {
+      const long long tc = tl + j < Nt ? tl + j : Nt - 1;
+      xt[j] = r_trg[tc * 3 + 0];
+      yt[j] = r_trg[tc * 3 + 1];
+      zt[j] = r_trg[tc * 3 + 2];
+      nt[j][0] = nt[j][1] = nt[j][2] = 0;
+      if (DOTN) {
+        nt[j][0] = n_trg[tc * 3 + 0];
+        nt[j][1] = n_trg[tc * 3 + 1];
+        nt[j][2] = n_trg[tc * 3 + 2];
+      }
+    }
+    const long long s_begin = slab_y * KMAT_SB;
+    const long long s_end = min(Ns, s_begin + KMAT_SB);
+    for (long long s = s_begin; s < s_end; s++) {
+      const Real xs = __ldg(r_src + s * 3 + 0), ys = __ldg(r_src + s * 3 + 1), zs = __ldg(r_src + s * 3 + 2);
+      Real n[3] = {0, 0, 0};
+#pragma unroll
+      for (int i = 0; i < ND; i++) n[i] = __ldg(n_src + s * ND + i);
+      const Real w = src_wts ? __ldg(src_wts + s) * scale : scale;
+      Real v[K0][V];
+#pragma unroll
+      for (int j = 0; j < V; j++) {
+        const Real dx = xt[j] - xs, dy = yt[j] - ys, dz = zt[j] - zs;
+        Real r2 = dx * dx;
+        r2 = fma(dy, dy, r2);
+        r2 = fma(dz, dz, r2);
+        const Real rinv = rsqrt_masked<NEWTON>(r2);
+        Real u[K0][K1];
+        Ker::matrix(u, dx, dy, dz, rinv, n);
+#pragma unroll
+        for (int k0 = 0; k0 < K0; k0++) {
+          if (DOTN) {
+            Real a = u[k0][0] * nt[j][0];
+            a = fma(u[k0][1 % K1], nt[j][1], a);
+            a = fma(u[k0][2 % K1], nt[j][2], a);
+            v[k0][j] = a * w;
+          } else {
+            v[k0][j] = u[k0][0] * w;
+          }
+        }
+      }
+#pragma unroll
+      for (int k0 = 0; k0 < K0; k0++) {
+        Real* dst = M + (size_t)(s * K0 + k0) * (size_t)Nt + (size_t)tl;  // ld = Nt (one value per target)
+        if (nvalid == V && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+          *reinterpret_cast<Vec*>(dst) = *reinterpret_cast<const Vec*>(v[k0]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < V; j++)
+            if (j < nvalid) dst[j] = v[k0][j];
+        }
+      }
+    }
+    return;
+  }
+
   Real(*slab)[SPAN] = reinterpret_cast<Real(*)[SPAN]>(slab_all + (size_t)warp * K0 * SPAN);
   const long long t0 = (tile_x * KMAT_WARPS + warp) * 32;  // first target of this warp
   if (t0 >= Nt) return;                                    // whole warp out of range (no CTA-wide sync below)
@@ -83,13 +162,7 @@ __device__ __forceinline__ void kmat_block(const Real* __restrict__ r_trg, const
       }
     }
     Real* row = M + (size_t)(s * K0) * (size_t)ld + (size_t)t0 * K1OUT;
-    if (K1OUT == 1) {
-      // a lane's element IS its position in the row: store directly, no transpose needed
-#pragma unroll
-      for (int k0 = 0; k0 < K0; k0++) {
-        if (lane < span_valid) row[(size_t)k0 * (size_t)ld + lane] = v[k0][0];
-      }
-    } else {
+    {
       __syncwarp();  // previous iteration's reads of the slab are complete
 #pragma unroll
       for (int k0 = 0; k0 < K0; k0++) {
@@ -147,7 +220,8 @@ __global__ void __launch_bounds__(KMAT_THREADS) kmat_batch_kernel(const Real* __
   const long long b = lo;
   const long long Nt = D.trg_dsp[b + 1] - D.trg_dsp[b];
   const long long Ns = D.src_dsp[b + 1] - D.src_dsp[b];
-  const long long ntx = (Nt + KMAT_THREADS - 1) / KMAT_THREADS;
+  constexpr int CT = kmat_cta_targets<Ker, Real, DOTN>();
+  const long long ntx = (Nt + CT - 1) / CT;
   const long long c = cta - D.cta_dsp[b];
   const long long so = D.src_dsp[b], to = D.trg_dsp[b];
   kmat_block<Ker, Real, NEWTON, DOTN>(r_trg + to * 3, r_src + so * 3, Ker::ND ? n_src + so * Ker::ND : nullptr, src_wts ? src_wts + so : nullptr,

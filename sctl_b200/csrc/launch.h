@@ -28,6 +28,7 @@ struct EvalEntry {
                                    long long Nt, long long Ns, double scale, int accumulate, int sms, cudaStream_t st);
   cudaError_t (*kmat[NUM_NEWTON])(const void* r_trg, const void* r_src, const void* n_src, void* M, long long Nt, long long Ns, double scale,
                                   cudaStream_t st);
+  int kmat_cta_targets[2];  // targets per CTA of the KernelMatrix kernels, [1] = with the target-normal contraction
   // batched small-block KernelMatrix; [1] = with the target-normal contraction (null when TrgDim is not a multiple of 3)
   cudaError_t (*kmat_batch[2][NUM_NEWTON])(const void* r_trg, const void* r_src, const void* n_src, const void* src_wts, const void* n_trg, void* M,
                                            const KmatBatchDesc& D, long long n_ctas, double scale, cudaStream_t st);

@@ -74,7 +74,7 @@ def test_eval_digits(checker, kid, dt, digits):
 
 @pytest.mark.parametrize("dt", DTYPES)
 @pytest.mark.parametrize("kid", range(8))
-@pytest.mark.parametrize("Nt,Ns", [(1, 37), (37, 1), (130, 67), (33, 200)])
+@pytest.mark.parametrize("Nt,Ns", [(1, 37), (37, 1), (130, 67), (33, 200), (516, 40), (1031, 33)])
 def test_kernel_matrix_matches_checker(checker, kid, dt, Nt, Ns):
     Xt, Xs, Xn, _ = _problem(kid, Nt, Ns, dt, coincident=8)
     want = checker.kernel_matrix(kid, Xt, Xs, Xn)

@@ -11,7 +11,7 @@ TAGS = {"f64": np.float64, "f32": np.float32}
 
 def kernel_files():
     fs = sorted(glob.glob(os.path.join(GOLDEN, "kernel*_*.npz")))
-    assert len(fs) == 8, "golden fixtures missing: run scripts/make_golden.py in the authoring container"
+    assert len(fs) == 8, "golden fixtures missing: run tests/tools/make_golden.py in the authoring container"
     return fs
 
 

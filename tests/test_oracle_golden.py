@@ -1,5 +1,5 @@
 """CPU: pins the oracle (C port, oracle/oracle_port.c) — and the C-ABI metadata — to golden vectors produced by the
-UNMODIFIED reference (scripts/make_golden.py -> tests/golden/). The reference ships no golden vectors for this path
+UNMODIFIED reference (tests/tools/make_golden.py -> tests/golden/). The reference ships no golden vectors for this path
 (SURVEY.md section 4), so its own outputs, generated here, are the pin."""
 import numpy as np
 import pytest

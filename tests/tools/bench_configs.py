@@ -2,7 +2,7 @@
 end-to-end (host buffers through the C ABI) pairs/s, FP pipe fraction, rel-L2 on a target subset vs the CPU reference."""
 import os, sys, time
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 from oracle import loader
 from sctl_b200 import KERNELS, capi, synth

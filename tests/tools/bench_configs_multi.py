@@ -5,7 +5,7 @@ rel-L2 of a target sample on every rank against the CPU reference (max over rank
 Usage: torchrun ... bench_configs_multi.py [C3 C4 C5] [--scale S]   (--scale divides N for a quick functional check)"""
 import os, sys
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 import torch.distributed as dist
 from oracle import loader

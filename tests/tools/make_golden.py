@@ -1,7 +1,7 @@
 """Generates tests/golden/*.npz from the UNMODIFIED reference (oracle/_ref/libsctl_ref_*.so, i.e. /root/reference's
 own GenericKernel::Eval / KernelMatrix / ParticleFMM::EvalDirect / approx_rsqrt compiled by oracle/Makefile).
 
-Run in the authoring container (needs /root/reference to have built oracle/_ref):  python scripts/make_golden.py
+Run in the authoring container (needs /root/reference to have built oracle/_ref):  python tests/tools/make_golden.py
 Inputs are NOT stored: they are regenerated from sctl_b200.synth with the recorded (Nt, Ns, seed, coincident).
 """
 import os
@@ -9,7 +9,7 @@ import sys
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from oracle import loader  # noqa: E402
 from sctl_b200 import synth  # noqa: E402

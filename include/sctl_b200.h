@@ -122,6 +122,7 @@ SCTL_B200_API int sctl_b200_kernel_matrix_batch(int kernel_id, int dtype, int64_
 SCTL_B200_API int sctl_b200_buf_create(void** d_ptr, int dtype, int64_t n);
 SCTL_B200_API int sctl_b200_buf_upload(void* d_ptr, const void* host, int dtype, int64_t n);
 SCTL_B200_API int sctl_b200_buf_download(const void* d_ptr, void* host, int dtype, int64_t n);
+SCTL_B200_API int sctl_b200_buf_zero(void* d_ptr, int dtype, int64_t n);                    /* Vector::SetZero (vector.txx) */
 SCTL_B200_API int sctl_b200_buf_destroy(void* d_ptr);
 
 /* Device-resident particle context — the GPU-aware counterpart of ParticleFMM's registry and EvalDirect

@@ -29,6 +29,7 @@ SYMBOLS = {
     "sctl_b200_kernel_matrix_batch": (c_int, [c_int, c_int, c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), c_void_p, c_void_p, c_void_p,
                                               c_void_p, c_void_p, c_void_p, c_int64, c_int, c_uint]),
     "sctl_b200_buf_create": (c_int, [POINTER(c_void_p), c_int, c_int64]),
+    "sctl_b200_buf_zero": (c_int, [c_void_p, c_int, c_int64]),
     "sctl_b200_buf_upload": (c_int, [c_void_p, c_void_p, c_int, c_int64]),
     "sctl_b200_buf_download": (c_int, [c_void_p, c_void_p, c_int, c_int64]),
     "sctl_b200_buf_destroy": (c_int, [c_void_p]),

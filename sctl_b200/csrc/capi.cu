@@ -1065,6 +1065,12 @@ int sctl_b200_buf_download(const void* d_ptr, void* host, int dtype, int64_t n) 
   if (n) CU_TRY(cudaMemcpy(host, d_ptr, (size_t)n * elem_size(dtype), cudaMemcpyDeviceToHost));
   return 0;
 }
+int sctl_b200_buf_zero(void* d_ptr, int dtype, int64_t n) {
+  if ((n > 0 && !d_ptr) || n < 0) return set_error(SCTL_B200_ERR_ARG, "bad argument");
+  if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return set_error(SCTL_B200_ERR_DTYPE, "unknown dtype %d", dtype);
+  if (n) CU_TRY(cudaMemset(d_ptr, 0, (size_t)n * elem_size(dtype)));
+  return 0;
+}
 int sctl_b200_buf_destroy(void* d_ptr) {
   if (d_ptr) CU_TRY(cudaFree(d_ptr));
   return 0;

@@ -15,6 +15,7 @@
 #include <sctl.hpp>
 #include <sctl_b200/generic-kernel-b200.hpp>
 #include <sctl_b200/particle-fmm-b200.hpp>
+#include <sctl_b200/device-vector-b200.hpp>
 
 #include <cmath>
 #include <cstdio>
@@ -188,6 +189,37 @@ int main(int argc, char** argv) {
     double worst = 0;
     for (Long b = 0; b < nb; b++) worst = std::max(worst, err[b]);
     report("KernelMatrix<double,true> from 32 OpenMP iterations (concurrent callers)", worst, 1e-12);
+  }
+  {  // device-resident Vector storage: upload once, Eval twice (overwrite, then accumulate), density update, KernelMatrix
+    using Cpu = sctl::GenericKernel<CpuCopy<sctl::kernel_impl::Stokes3D_DxU>>;
+    const Long Nt = 3001, Ns = 2500;
+    sctl::Vector<double> Xt(Nt * 3), Xs(Ns * 3), Xn(Ns * 3), F(Ns * 3), F2(Ns * 3), U, Uref;
+    fill(Xt), fill(Xs), fill(Xn), fill(F), fill(F2);
+    sctl::Stokes3D_DxU gpu;
+    Cpu cpu;
+    sctl_b200::DeviceVector<double> dXt(Xt), dXs(Xs), dXn(Xn), dF(F), dU;
+    sctl_b200::Eval(gpu, dU, dXt, dXs, dXn, dF);  // dU is resized: overwritten
+    dF = F2;                                       // only the density crosses the bus
+    sctl_b200::Eval(gpu, dU, dXt, dXs, dXn, dF);  // accumulated
+    dU.CopyTo(U);
+    cpu.Eval<double, false>(Uref, Xt, Xs, Xn, F);
+    cpu.Eval<double, false>(Uref, Xt, Xs, Xn, F2);
+    report("DeviceVector<double>: Eval + density update + accumulate", rel_l2(U, Uref), 1e-12);
+    dU.SetZero();
+    dU.CopyTo(U);
+    double nz = 0;
+    for (Long i = 0; i < U.Dim(); i++) nz += std::fabs(U[i]);
+    report("DeviceVector<double>::SetZero", nz, 1e-300);
+    sctl_b200::DeviceVector<float> fXt, fXs, fXn, fM;
+    sctl::Vector<float> Xtf(61 * 3), Xsf(37 * 3), Xnf(37 * 3), Mh;
+    fill(Xtf), fill(Xsf), fill(Xnf);
+    fXt = Xtf; fXs = Xsf; fXn = Xnf;
+    sctl_b200::KernelMatrix(gpu, fM, fXt, fXs, fXn);
+    fM.CopyTo(Mh);
+    sctl::Matrix<float> Mref;
+    cpu.KernelMatrix<float, false>(Mref, Xtf, Xsf, Xnf);
+    const sctl::Vector<float> c(Mref.Dim(0) * Mref.Dim(1), Mref.begin(), false);
+    report("DeviceVector<float>: KernelMatrix", rel_l2(Mh, c), 1e-5);
   }
   std::printf("launches issued by libsctl_b200: %lld\n", (long long)sctl_b200_launch_count());
   std::printf(g_fail ? "SHIM TEST FAILED (%d)\n" : "SHIM TEST PASSED\n", g_fail);

@@ -91,3 +91,46 @@ def test_full_size_f32_16M_sources(checker):
     torch.cuda.synchronize()
     err = _subset_check(checker, kid, Xt, Xs, Xn, F, U.cpu().numpy(), 1e-5)
     print(f"C5 f32 16M sources: rel-L2 vs f64 reference = {err:.3e}")
+
+
+def test_more_than_2_31_output_elements(checker):
+    """Maximum-size indexing: Stokes3D_FxT f32 on 240M targets x 300 sources writes 2.16e9 values (> 2^31) - every
+    target / output offset in the kernels must be 64-bit. Inputs are generated on the device (11.5 GB in all); the first and
+    last targets are compared with the CPU reference."""
+    import torch
+
+    kid, Nt, Ns = 5, 240_000_000, 300
+    free, _ = torch.cuda.mem_get_info()
+    if free < 16e9:
+        pytest.skip("needs 16 GB of free device memory")
+    d = capi.kernel_dims(kid)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    Xt = torch.rand(Nt * 3, dtype=torch.float32, device="cuda", generator=g) - 0.5
+    Xs = torch.rand(Ns * 3, dtype=torch.float32, device="cuda", generator=g) - 0.5
+    F = torch.rand(Ns * 3, dtype=torch.float32, device="cuda", generator=g) - 0.5
+    U = KERNELS[kid]().Eval(None, Xt, Xs, None, F)
+    torch.cuda.synchronize()
+    assert U.numel() == Nt * d["trg_dim"] > 2**31
+    f64 = lambda a: a.cpu().numpy().astype(np.float64)
+    for lo, hi in ((0, 40), (Nt // 2 + 3, Nt // 2 + 43), (Nt - 40, Nt)):
+        want = checker.eval(kid, f64(Xt[3 * lo:3 * hi]), f64(Xs), None, f64(F))
+        got = f64(U[9 * lo:9 * hi])
+        assert rel_l2(got, want) <= TOL[np.dtype(np.float32)], (lo, hi)
+    del U, Xt
+    torch.cuda.empty_cache()
+
+
+def test_fifty_million_sources_few_targets(checker):
+    """Maximum-size indexing on the source side: 50M sources (195313 tiles, more than the 65535 chunk rows a grid may
+    have) x 64 targets, Stokes3D_FxU f64; record offsets and tile counters must be 64-bit / clamp correctly."""
+    import torch
+
+    kid, Nt, Ns = 3, 64, 50_000_000
+    g = torch.Generator(device="cuda").manual_seed(12)
+    Xt = torch.rand(Nt * 3, dtype=torch.float64, device="cuda", generator=g) - 0.5
+    Xs = torch.rand(Ns * 3, dtype=torch.float64, device="cuda", generator=g) - 0.5
+    F = torch.rand(Ns * 3, dtype=torch.float64, device="cuda", generator=g) - 0.5
+    U = KERNELS[kid]().Eval(None, Xt, Xs, None, F)
+    torch.cuda.synchronize()
+    want = checker.eval(kid, Xt.cpu().numpy(), Xs.cpu().numpy(), None, F.cpu().numpy())
+    assert rel_l2(U.cpu().numpy(), want) <= TOL[np.dtype(np.float64)]

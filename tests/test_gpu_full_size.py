@@ -134,3 +134,28 @@ def test_fifty_million_sources_few_targets(checker):
     torch.cuda.synchronize()
     want = checker.eval(kid, Xt.cpu().numpy(), Xs.cpu().numpy(), None, F.cpu().numpy())
     assert rel_l2(U.cpu().numpy(), want) <= TOL[np.dtype(np.float64)]
+
+
+def test_kernel_matrix_more_than_2_31_elements(checker):
+    """KernelMatrix with 2.25e9 entries (Stokes3D_DxU f32, 5000 sources x 50000 targets, 9 GB): row offsets must be
+    64-bit. Blocks at the start, middle and far end of M are compared with the CPU reference."""
+    import torch
+
+    kid, Nt, Ns = 4, 50_000, 5_000
+    free, _ = torch.cuda.mem_get_info()
+    if free < 12e9:
+        pytest.skip("needs 12 GB of free device memory")
+    g = torch.Generator(device="cuda").manual_seed(13)
+    Xt = torch.rand(Nt * 3, dtype=torch.float32, device="cuda", generator=g) - 0.5
+    Xs = torch.rand(Ns * 3, dtype=torch.float32, device="cuda", generator=g) - 0.5
+    Xn = torch.rand(Ns * 3, dtype=torch.float32, device="cuda", generator=g) - 0.5
+    M = KERNELS[kid]().KernelMatrix(Xt, Xs, Xn)
+    torch.cuda.synchronize()
+    assert M.shape == (Ns * 3, Nt * 3) and M.numel() > 2**31
+    f64 = lambda a: a.cpu().numpy().astype(np.float64)
+    for s0, t0 in ((0, 0), (Ns // 2, Nt // 2 + 1), (Ns - 4, Nt - 7)):
+        want = checker.kernel_matrix(kid, f64(Xt[3 * t0:3 * (t0 + 7)]), f64(Xs[3 * s0:3 * (s0 + 4)]), f64(Xn[3 * s0:3 * (s0 + 4)]))
+        got = f64(M[3 * s0:3 * (s0 + 4), 3 * t0:3 * (t0 + 7)])
+        assert rel_l2(got, want) <= TOL[np.dtype(np.float32)], (s0, t0)
+    del M
+    torch.cuda.empty_cache()

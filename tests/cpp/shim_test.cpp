@@ -16,6 +16,7 @@
 #include <sctl_b200/generic-kernel-b200.hpp>
 #include <sctl_b200/particle-fmm-b200.hpp>
 #include <sctl_b200/device-vector-b200.hpp>
+#include <sctl_b200/kernel-matrix-batch-b200.hpp>
 
 #include <cmath>
 #include <cstdio>
@@ -189,6 +190,47 @@ int main(int argc, char** argv) {
     double worst = 0;
     for (Long b = 0; b < nb; b++) worst = std::max(worst, err[b]);
     report("KernelMatrix<double,true> from 32 OpenMP iterations (concurrent callers)", worst, 1e-12);
+  }
+  {  // all per-element blocks of a SetupNear-like sweep in one launch, with the call site's row scaling / target-normal contraction
+    using Cpu = sctl::GenericKernel<CpuCopy<sctl::kernel_impl::Stokes3D_FxT>>;
+    sctl::Stokes3D_FxT gpu;
+    Cpu cpu;
+    const Long nb = 17;
+    sctl::Vector<Long> near_dsp(nb + 1), far_dsp(nb + 1);
+    near_dsp[0] = far_dsp[0] = 0;
+    for (Long b = 0; b < nb; b++) {
+      near_dsp[b + 1] = near_dsp[b] + (b % 5 == 3 ? 0 : 7 + 31 * (b % 7));  // some elements have no near targets
+      far_dsp[b + 1] = far_dsp[b] + 5 + 9 * (b % 4);
+    }
+    sctl::Vector<double> Xt(near_dsp[nb] * 3), Xnt(near_dsp[nb] * 3), Xs(far_dsp[nb] * 3), Xn, W(far_dsp[nb]);
+    fill(Xt), fill(Xnt), fill(Xs), fill(W);
+    for (int dotn = 0; dotn < 2; dotn++) {
+      sctl::Vector<double> M;
+      sctl::Vector<Long> M_dsp;
+      sctl_b200::KernelMatrixBatch(gpu, M, M_dsp, near_dsp, far_dsp, Xt, Xs, Xn, W, dotn ? Xnt : sctl::Vector<double>());
+      double worst = 0;
+      for (Long b = 0; b < nb; b++) {
+        const Long nt = near_dsp[b + 1] - near_dsp[b], ns = far_dsp[b + 1] - far_dsp[b];
+        if (!nt) continue;
+        const sctl::Vector<double> xt(nt * 3, Xt.begin() + near_dsp[b] * 3, false), xs(ns * 3, Xs.begin() + far_dsp[b] * 3, false);
+        sctl::Matrix<double> Mref;
+        cpu.KernelMatrix<double, false>(Mref, xt, xs, Xn);
+        const Long k1o = dotn ? 3 : 9;
+        sctl::Vector<double> want(ns * 3 * nt * k1o);
+        for (Long s = 0; s < ns; s++)
+          for (Long k0 = 0; k0 < 3; k0++)
+            for (Long t = 0; t < nt; t++)
+              for (Long k1 = 0; k1 < k1o; k1++) {
+                double v = 0;  // boundary_integral.txx:968-997
+                if (dotn) for (Long l = 0; l < 3; l++) v += Mref[s * 3 + k0][(t * 3 + k1) * 3 + l] * W[far_dsp[b] + s] * Xnt[(near_dsp[b] + t) * 3 + l];
+                else v = Mref[s * 3 + k0][t * 9 + k1] * W[far_dsp[b] + s];
+                want[(s * 3 + k0) * (nt * k1o) + t * k1o + k1] = v;
+              }
+        const sctl::Vector<double> got(want.Dim(), M.begin() + M_dsp[b], false);
+        worst = std::max(worst, rel_l2(got, want));
+      }
+      report(dotn ? "KernelMatrixBatch<Stokes3D_FxT>: 17 blocks, weights + target-normal contraction" : "KernelMatrixBatch<Stokes3D_FxT>: 17 blocks, weights", worst, 1e-12);
+    }
   }
   {  // device-resident Vector storage: upload once, Eval twice (overwrite, then accumulate), density update, KernelMatrix
     using Cpu = sctl::GenericKernel<CpuCopy<sctl::kernel_impl::Stokes3D_DxU>>;

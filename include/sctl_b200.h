@@ -160,6 +160,12 @@ SCTL_B200_API int sctl_b200_device_count(int* n);
 SCTL_B200_API int sctl_b200_set_device(int dev);
 SCTL_B200_API int sctl_b200_get_device(int* dev);
 SCTL_B200_API int sctl_b200_sm_count(int* n);
+/* In-process multi-GPU driver (SCTL_B200_ALL_GPUS). sctl_b200_init selects the devices the flag shards over (ndev == 0 or
+ * dev_ids == NULL: every visible device, the default without a call) and creates their CUDA contexts up front, so the first
+ * Eval does not pay for it; sctl_b200_finalize waits for those devices, releases the calling thread's streams, events and
+ * staging blocks and forgets the selection. Both are optional: every entry point initialises lazily. */
+SCTL_B200_API int sctl_b200_init(int ndev, const int* dev_ids);
+SCTL_B200_API int sctl_b200_finalize(void);
 
 /* Measurement helpers (bench.py): number of kernel launches this library has issued from this process, and a
  * register-resident DFMA / FFMA chain that measures the CUDA-core FP64 / FP32 peak used as roofline

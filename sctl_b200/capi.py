@@ -50,6 +50,8 @@ SYMBOLS = {
     "sctl_b200_fmm_eval_direct": (c_int, [c_void_p, c_char_p, c_void_p, c_int64, c_uint]),
     "sctl_b200_device_count": (c_int, [POINTER(c_int)]),
     "sctl_b200_set_device": (c_int, [c_int]),
+    "sctl_b200_init": (c_int, [c_int, POINTER(c_int)]),
+    "sctl_b200_finalize": (c_int, []),
     "sctl_b200_get_device": (c_int, [POINTER(c_int)]),
     "sctl_b200_sm_count": (c_int, [POINTER(c_int)]),
     "sctl_b200_launch_count": (c_int64, []),

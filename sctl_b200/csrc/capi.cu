@@ -84,6 +84,8 @@ struct DevCtx {
 };
 constexpr size_t STAGE_BYTES = 1u << 20;
 static thread_local std::vector<DevCtx> t_ctx;
+static std::mutex g_devices_mutex;
+static std::vector<int> g_devices;  // devices SCTL_B200_ALL_GPUS shards over (sctl_b200_init); empty = every visible device
 static std::mutex g_pool_mutex;
 static std::vector<int> g_pool_configured;
 
@@ -426,9 +428,22 @@ static int eval_host_all_gpus(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
     cudaGetLastError();
     return set_error(SCTL_B200_ERR_CUDA, "no usable CUDA device; libsctl_b200 has no CPU fallback");
   }
-  if (ndev == 1 || Nt < ndev) return eval_host_one_device(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, v_src, v_trg, digits, accumulate);
+  std::vector<int> devs;
+  {
+    std::lock_guard<std::mutex> lk(g_devices_mutex);
+    devs = g_devices;
+  }
+  if (devs.empty())
+    for (int g = 0; g < ndev; g++) devs.push_back(g);
+  ndev = (int)devs.size();
   int dev0 = 0;
   CU_TRY(cudaGetDevice(&dev0));
+  if (ndev == 1 || Nt < ndev) {
+    if (ndev == 1 && devs[0] != dev0) CU_TRY(cudaSetDevice(devs[0]));
+    const int rc1 = eval_host_one_device(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, v_src, v_trg, digits, accumulate);
+    if (ndev == 1 && devs[0] != dev0) cudaSetDevice(dev0);
+    return rc1;
+  }
   const KernelInfo& ki = KINFO[kernel_id];
   const size_t esz = elem_size(dtype);
   std::vector<int> rcs(ndev, 0);
@@ -436,7 +451,7 @@ static int eval_host_all_gpus(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
   std::vector<std::thread> th;
   for (int g = 0; g < ndev; g++) {
     th.emplace_back([&, g]() {
-      if (cudaSetDevice(g) != cudaSuccess) {
+      if (cudaSetDevice(devs[g]) != cudaSuccess) {
         rcs[g] = SCTL_B200_ERR_CUDA;
         msgs[g] = "cudaSetDevice failed";
         return;
@@ -451,7 +466,7 @@ static int eval_host_all_gpus(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
   for (auto& t : th) t.join();
   cudaSetDevice(dev0);
   for (int g = 0; g < ndev; g++)
-    if (rcs[g]) return set_error(rcs[g], "device %d: %s", g, msgs[g].c_str());
+    if (rcs[g]) return set_error(rcs[g], "device %d: %s", devs[g], msgs[g].c_str());
   return 0;
 }
 
@@ -1086,6 +1101,60 @@ int sctl_b200_device_count(int* n) {
     return cuda_error(e, "cudaGetDeviceCount");
   }
   *n = c;
+  return 0;
+}
+int sctl_b200_init(int ndev, const int* dev_ids) {
+  int visible = 0;
+  cudaError_t e = cudaGetDeviceCount(&visible);
+  if (e != cudaSuccess || visible < 1) {
+    cudaGetLastError();
+    return set_error(SCTL_B200_ERR_CUDA, "no usable CUDA device (%s); libsctl_b200 has no CPU fallback",
+                     e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  }
+  if (ndev < 0) return set_error(SCTL_B200_ERR_ARG, "negative device count");
+  std::vector<int> devs;
+  if (ndev == 0 || !dev_ids) {
+    for (int g = 0; g < visible; g++) devs.push_back(g);
+  } else {
+    for (int i = 0; i < ndev; i++) {
+      if (dev_ids[i] < 0 || dev_ids[i] >= visible) return set_error(SCTL_B200_ERR_ARG, "device id %d out of range (0..%d)", dev_ids[i], visible - 1);
+      for (int d : devs)
+        if (d == dev_ids[i]) return set_error(SCTL_B200_ERR_ARG, "device id %d listed twice", dev_ids[i]);
+      devs.push_back(dev_ids[i]);
+    }
+  }
+  int dev0 = 0;
+  CU_TRY(cudaGetDevice(&dev0));
+  for (int d : devs) {  // create the contexts now
+    CU_TRY(cudaSetDevice(d));
+    CU_TRY(cudaFree(nullptr));
+  }
+  CU_TRY(cudaSetDevice(dev0));
+  std::lock_guard<std::mutex> lk(g_devices_mutex);
+  g_devices = (ndev == 0 || !dev_ids) ? std::vector<int>() : devs;
+  return 0;
+}
+int sctl_b200_finalize(void) {
+  std::vector<int> devs;
+  {
+    std::lock_guard<std::mutex> lk(g_devices_mutex);
+    devs.swap(g_devices);
+  }
+  int visible = 0;
+  if (cudaGetDeviceCount(&visible) != cudaSuccess || visible < 1) {
+    cudaGetLastError();
+    return 0;  // nothing was ever initialised
+  }
+  int dev0 = 0;
+  CU_TRY(cudaGetDevice(&dev0));
+  if (devs.empty())
+    for (auto& c : t_ctx) devs.push_back(c.dev);
+  for (int d : devs) {
+    if (cudaSetDevice(d) == cudaSuccess) cudaDeviceSynchronize();
+  }
+  release_thread_ctx();
+  cudaGetLastError();
+  CU_TRY(cudaSetDevice(dev0));
   return 0;
 }
 int sctl_b200_set_device(int dev) {

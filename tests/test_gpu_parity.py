@@ -121,3 +121,29 @@ def test_eval_all_gpus_flag(checker, kid, dt):
     want = checker.eval(kid, Xt, Xs, Xn, F, v_trg=U0.copy())
     got = KERNELS[kid]().Eval(U0.copy(), Xt, Xs, Xn, F, all_gpus=True)
     assert rel_l2(got, want) <= TOL[np.dtype(dt)]
+
+
+def test_init_finalize(checker):
+    """sctl_b200_init selects the devices SCTL_B200_ALL_GPUS shards over; finalize releases the thread's streams and staging
+    blocks; every entry point re-initialises lazily afterwards."""
+    import ctypes
+
+    L = capi.lib()
+    n = capi.device_count()
+    ids = (ctypes.c_int * 1)(0)
+    capi.check(L.sctl_b200_init(1, ids))
+    Xt, Xs, Xn, F = _problem(3, 5000, 9000, np.float64)
+    want = checker.eval(3, Xt, Xs, Xn, F)
+    got = KERNELS[3]().Eval(None, Xt, Xs, Xn, F, all_gpus=True)  # one selected device
+    assert rel_l2(got, want) <= TOL[np.dtype(np.float64)]
+    capi.check(L.sctl_b200_finalize())
+    got = KERNELS[3]().Eval(None, Xt, Xs, Xn, F)  # lazily re-initialised
+    assert rel_l2(got, want) <= TOL[np.dtype(np.float64)]
+    bad = (ctypes.c_int * 1)(n)
+    assert L.sctl_b200_init(1, bad) != 0 and b"out of range" in L.sctl_b200_last_error()
+    twice = (ctypes.c_int * 2)(0, 0)
+    assert L.sctl_b200_init(2, twice) != 0
+    capi.check(L.sctl_b200_init(0, None))  # back to "every visible device"
+    got = KERNELS[3]().Eval(None, Xt, Xs, Xn, F, all_gpus=True)
+    assert rel_l2(got, want) <= TOL[np.dtype(np.float64)]
+    capi.check(L.sctl_b200_finalize())

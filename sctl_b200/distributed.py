@@ -40,6 +40,31 @@ def partition(n: int, rank: int, size: int) -> tuple[int, int]:
     return n * rank // size, n * (rank + 1) // size
 
 
+def allgather_blocks(local, width, counts, rank, size, group=None, out=None):
+    """Contiguous replica of every rank's block of an AoS array with `width` values per particle: ONE all_gather_into_tensor
+    when the blocks are equal (ncclAllGather), a chain of in-place broadcasts when they are ragged. `out` (optional) is
+    reused when large enough."""
+    total = width * sum(counts)
+    if local.numel() != width * counts[rank]:
+        raise ValueError(f"expected {width} values for each of this rank's {counts[rank]} particles, got {local.numel()}")
+    if out is None or out.numel() < total or out.dtype != local.dtype or out.device != local.device:
+        out = torch.empty(max(total, 1), dtype=local.dtype, device=local.device)
+    out = out[:total]
+    if total == 0:
+        return out
+    if len(set(counts)) == 1:
+        dist.all_gather_into_tensor(out, local.reshape(-1), group=group)
+        return out
+    off = [0]
+    for c in counts:
+        off.append(off[-1] + width * c)
+    out[off[rank]:off[rank + 1]].copy_(local.reshape(-1))
+    for r in range(size):
+        if counts[r]:
+            dist.broadcast(out[off[r]:off[r + 1]], src=dist.get_global_rank(group, r) if group is not None else r, group=group)
+    return out
+
+
 class ShardedDirectSum:
     """Direct summation with targets and sources sharded over the ranks of a process group."""
 
@@ -98,21 +123,11 @@ class ShardedDirectSum:
         return self._call_ring(U, Xt, Xs, Xn if Nd else None, F, digits, counts, rank, size)
 
     def _allgather(self, key, local, width, counts, rank, size):
-        """contiguous replica of every rank's block of one AoS array (width values per source)"""
-        total = sum(counts)
-        out = self._buf(key, width * total, local)
-        if total == 0:
-            return out
-        if len(set(counts)) == 1:
-            dist.all_gather_into_tensor(out, local.reshape(-1), group=self.group)  # one ncclAllGather
-        else:  # ragged blocks (N not divisible by the group size): in-place chain of broadcasts into the replica
-            off = [0]
-            for c in counts:
-                off.append(off[-1] + width * c)
-            out[off[rank]:off[rank + 1]].copy_(local.reshape(-1))
-            for r in range(size):
-                if counts[r]:
-                    dist.broadcast(out[off[r]:off[r + 1]], src=self._global(r), group=self.group)
+        """contiguous replica of every rank's block of one AoS array (width values per source), in a reused buffer"""
+        out = allgather_blocks(local, width, counts, rank, size, self.group, self._bufs.get(key))
+        if out.numel():
+            base = out._base if out._base is not None else out
+            self._bufs[key] = base
         return out
 
     def _call_gather(self, U, Xt, Xs, Xn, F, digits, counts, rank, size):
@@ -252,22 +267,7 @@ class ShardedParticleFMM:
         rank, size = self._world()
         if size == 1:
             return local
-        if local.numel() != width * counts[rank]:
-            raise ValueError(f"expected {width} values for each of this rank's {counts[rank]} particles, got {local.numel()}")
-        out = torch.empty(width * sum(counts), dtype=local.dtype, device=local.device)
-        if out.numel() == 0:
-            return out
-        if len(set(counts)) == 1:
-            dist.all_gather_into_tensor(out, local, group=self.group)
-        else:
-            off = [0]
-            for c in counts:
-                off.append(off[-1] + width * c)
-            out[off[rank]:off[rank + 1]].copy_(local)
-            for r in range(size):
-                if counts[r]:
-                    dist.broadcast(out[off[r]:off[r + 1]], src=dist.get_global_rank(self.group, r) if self.group is not None else r, group=self.group)
-        return out
+        return allgather_blocks(local, width, counts, rank, size, self.group)
 
     # -- registry: identical on every rank (fmm-wrapper.txx:240-443) ---------------------------------------------
     def SetAccuracy(self, digits):

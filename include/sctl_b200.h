@@ -122,7 +122,7 @@ SCTL_B200_API int sctl_b200_kernel_matrix_batch(int kernel_id, int dtype, int64_
 SCTL_B200_API int sctl_b200_buf_create(void** d_ptr, int dtype, int64_t n);
 SCTL_B200_API int sctl_b200_buf_upload(void* d_ptr, const void* host, int dtype, int64_t n);
 SCTL_B200_API int sctl_b200_buf_download(const void* d_ptr, void* host, int dtype, int64_t n);
-SCTL_B200_API int sctl_b200_buf_zero(void* d_ptr, int dtype, int64_t n);                    /* Vector::SetZero (vector.txx) */
+SCTL_B200_API int sctl_b200_buf_zero(void* d_ptr, int dtype, int64_t n);                    /* Vector::SetZero (vector.txx:163) */
 SCTL_B200_API int sctl_b200_buf_destroy(void* d_ptr);
 
 /* Device-resident particle context — the GPU-aware counterpart of ParticleFMM's registry and EvalDirect
@@ -160,7 +160,8 @@ SCTL_B200_API int sctl_b200_device_count(int* n);
 SCTL_B200_API int sctl_b200_set_device(int dev);
 SCTL_B200_API int sctl_b200_get_device(int* dev);
 SCTL_B200_API int sctl_b200_sm_count(int* n);
-/* In-process multi-GPU driver (SCTL_B200_ALL_GPUS). sctl_b200_init selects the devices the flag shards over (ndev == 0 or
+/* In-process multi-GPU driver (SCTL_B200_ALL_GPUS); plays the role of the communicator handed to ParticleFMM(comm)
+ * (fmm-wrapper.txx:204, fmm-wrapper.hpp:45) for the target partition of EvalDirect (fmm-wrapper.txx:504-510). sctl_b200_init selects the devices the flag shards over (ndev == 0 or
  * dev_ids == NULL: every visible device, the default without a call) and creates their CUDA contexts up front, so the first
  * Eval does not pay for it; sctl_b200_finalize waits for those devices, releases the calling thread's streams, events and
  * staging blocks and forgets the selection. Both are optional: every entry point initialises lazily. */

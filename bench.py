@@ -42,7 +42,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n", type=int, default=int(os.environ.get("SCTL_B200_BENCH_N", 4_000_000)), help="Ns = Nt (default 4M = config C3)")
-    ap.add_argument("--e2e-steps", type=int, default=1)
+    ap.add_argument("--e2e-steps", type=int, default=3, help="end-to-end samples; the MEDIAN is reported")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of one reference sample")
     return ap.parse_args()
@@ -153,24 +153,82 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------------------
 # CPU reference arm / baseline: the reference's own Eval<double,true> (oracle/_ref) on all host threads
 # ------------------------------------------------------------------------------------------------------------
+HOST_THREADS = None  # (count, how): taken in main() BEFORE an OpenMP runtime is loaded (binding narrows the main thread's mask to one core)
+
+
+def host_threads() -> tuple[int, str, int]:
+    """Threads for the CPU arm: every PHYSICAL core this process may run on, whatever OMP_NUM_THREADS
+    says - torch.distributed.run exports OMP_NUM_THREADS=1 to its workers, which is not a statement about the host.
+    SCTL_B200_CPU_THREADS overrides."""
+    forced = os.environ.get("SCTL_B200_CPU_THREADS")
+    if forced and forced.isdigit() and int(forced) > 0:
+        return int(forced), "SCTL_B200_CPU_THREADS", int(forced)
+    try:
+        allowed = os.sched_getaffinity(0)
+    except AttributeError:
+        allowed = set(range(os.cpu_count() or 1))
+    cores = set()
+    try:
+        cpu = phys = core = None
+        with open("/proc/cpuinfo") as f:
+            for line in f.read().split("\n") + [""]:
+                if not line.strip():
+                    if cpu is not None and cpu in allowed:
+                        cores.add((phys, core if core is not None else cpu))
+                    cpu = phys = core = None
+                    continue
+                k, _, v = line.partition(":")
+                k, v = k.strip(), v.strip()
+                if k == "processor":
+                    cpu = int(v)
+                elif k == "physical id":
+                    phys = int(v)
+                elif k == "core id":
+                    core = int(v)
+    except (OSError, ValueError):
+        cores = set()
+    if cores:
+        return len(cores), f"physical cores among the {len(allowed)} logical CPUs of the affinity mask (/proc/cpuinfo)", len(allowed)
+    return max(1, len(allowed)), "logical CPUs of the affinity mask", max(1, len(allowed))
+
+
 def cpu_sample_runner(n: int, seconds: float):
     """Returns (run(), pairs_per_call, info): run() evaluates a bounded sample of the workload — the first T targets
-    against ALL n sources — with the reference's OpenMP+SIMD Eval (or the C port when oracle/_ref is absent)."""
+    against ALL n sources — with the reference's OpenMP+SIMD Eval (or the C port when oracle/_ref is absent). Never touches
+    the product library: the kernel dims come from the checker itself."""
     from oracle import loader
-    from sctl_b200 import capi, synth
+    from sctl_b200 import synth  # input generator only (numpy); loads no native code
 
     chk = loader.best()
-    d = capi.kernel_dims(KERNEL_ID) if os.path.exists(capi.LIB_PATH) else chk.kernel_dims(KERNEL_ID)
-    cores = chk.max_threads() if chk.kind == "reference" else (os.cpu_count() or 1)
+    d = chk.kernel_dims(KERNEL_ID)
+    cores, how, logical = HOST_THREADS or host_threads()
     _, Xs, _, F = synth.make_problem(d, 1, n, np.float64, coincident=0)
-    # calibrate on a small slab, then size T for ~`seconds` of CPU work
+
+    def calibrate(threads):
+        """pairs/s on a small slab (64 targets per thread x all sources) with `threads` threads"""
+        if chk.kind == "reference":
+            chk.set_threads(threads)  # omp_set_num_threads: overrides a torchrun-injected OMP_NUM_THREADS=1
+        Tc = 64 * threads
+        Xt = synth.uniform(synth.STREAM_TRG, 0, 3 * Tc)
+        chk.eval(KERNEL_ID, Xt[: 3 * 16], Xs[: 3 * 1000], None, F[: 3 * 1000])  # start the thread pool
+        chk.eval(KERNEL_ID, Xt, Xs, None, F)  # warm (page faults, thread pool)
+        t0 = time.perf_counter()
+        chk.eval(KERNEL_ID, Xt, Xs, None, F)
+        return Tc * n / (time.perf_counter() - t0)
+
+    if chk.kind == "reference":
+        # "all the host threads it can use": one per physical core (BASELINE.md section 3) or one per logical CPU, whichever
+        # the reference's Eval runs faster with on this host
+        trial = {t: calibrate(t) for t in sorted({cores, logical})}
+        cores = max(trial, key=trial.get)
+        rate = trial[cores]
+        chk.set_threads(cores)
+        assert chk.max_threads() == cores
+        how += "; calibrated " + ", ".join(f"{t} threads: {r:.3g} pairs/s" for t, r in trial.items())
+    else:
+        os.environ["OMP_NUM_THREADS"] = str(cores)
+        rate = calibrate(cores)
     Tc = 64 * cores
-    Xt = synth.uniform(synth.STREAM_TRG, 0, 3 * Tc)
-    chk.eval(KERNEL_ID, Xt[: 3 * 16], Xs[: 3 * 1000], None, F[: 3 * 1000])  # start the thread pool
-    chk.eval(KERNEL_ID, Xt, Xs, None, F)  # warm (page faults, thread pool)
-    t0 = time.perf_counter()
-    chk.eval(KERNEL_ID, Xt, Xs, None, F)
-    rate = Tc * n / (time.perf_counter() - t0)
     T = int(max(Tc, min(n, rate * seconds / n)))
     T = (T // (8 * cores)) * (8 * cores) or Tc
     Xt = synth.uniform(synth.STREAM_TRG, 0, 3 * T)
@@ -181,7 +239,8 @@ def cpu_sample_runner(n: int, seconds: float):
         chk.eval(KERNEL_ID, Xt, Xs, None, F, v_trg=U)
         return U
 
-    info = {"kind": chk.kind, "cores": cores, "sample": f"first {T} of {n} targets x all {n} sources, Stokes3D_FxU f64, "
+    info = {"kind": chk.kind, "cores": cores, "threads_from": how, "omp_proc_bind": os.environ.get("OMP_PROC_BIND"), "omp_places": os.environ.get("OMP_PLACES"),
+            "sample": f"first {T} of {n} targets x all {n} sources, Stokes3D_FxU f64, "
             f"{'reference Eval<double,true> OpenMP+Vec (' + os.path.basename(chk.path) + ')' if chk.kind == 'reference' else 'C port (oracle_port.c), OpenMP'}"}
     return run, T * n, info
 
@@ -328,13 +387,16 @@ def run_b200_arm(args):
     e2e_step()  # warm-up (first host-path call creates the library stream / pool)
     barrier()
     l1 = capi.launch_count()
-    w0 = time.perf_counter()
-    for _ in range(args.e2e_steps):
+    e2e_samples = []
+    for _ in range(max(1, args.e2e_steps)):
+        barrier()
+        w0 = time.perf_counter()
         e2e_step()
-    torch.cuda.synchronize()
-    e2e_ms = allmax((time.perf_counter() - w0) * 1e3 / args.e2e_steps)
+        torch.cuda.synchronize()
+        e2e_samples.append(allmax((time.perf_counter() - w0) * 1e3))  # max over ranks of each step, then the median of the steps
+    e2e_ms = statistics.median(e2e_samples)
     barrier()
-    launches_e2e = int(allsum(capi.launch_count() - l1))
+    launches_e2e = int(allsum(capi.launch_count() - l1)) // max(1, args.e2e_steps)
     if world == 1:
         eval_ms_kernel = capi.last_timing()["eval_ms"]
     e2e_value = float(n) * float(n) / (e2e_ms * 1e-3)
@@ -361,10 +423,10 @@ def run_b200_arm(args):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args), "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
-                    "steps": args.e2e_steps, "gpu_launches": launches_e2e,
+                    "steps": args.e2e_steps, "ms_samples": e2e_samples, "statistic": "median of the per-step max over ranks", "gpu_launches_per_step": launches_e2e,
                     "api": "sctl_b200_eval (host pointers, C ABI)" if world == 1 else "ShardedDirectSum (pinned host shards -> NCCL -> eval -> host)"},
             "gpu_launches": launches, "roofline": roofline, "parity": parity}
-    if not args.no_cpu_baseline and world == 1:
+    if not args.no_cpu_baseline:  # rank 0 only (the other ranks have left), at every N: the CPU path timed beside the GPU number
         run, pairs, info = cpu_sample_runner(n, args.cpu_seconds)
         run()
         c0 = time.perf_counter()
@@ -377,6 +439,14 @@ def run_b200_arm(args):
 
 def main():
     args = parse_args()
+    # the CPU arm runs with OMP_PROC_BIND=close OMP_PLACES=cores. The OpenMP runtime reads these when it
+    # is loaded, so they are set before anything imports it (an explicit setting of the caller wins).
+    global HOST_THREADS
+    HOST_THREADS = host_threads()
+    # Only on the rank that runs CPU work: binding pins the initial thread to the first place, and N ranks must not share one core.
+    if int(os.environ.get("RANK", "0")) == 0:
+        os.environ.setdefault("OMP_PROC_BIND", "close")
+        os.environ.setdefault("OMP_PLACES", "cores")
     # stdout carries exactly ONE JSON line: everything libraries print while we run (e.g. "NCCL version ..." from the first
     # communicator) is sent to stderr, and print() below writes to the saved descriptor.
     sys.stdout.flush()

@@ -17,8 +17,9 @@
  *  - Plain C types only. All arrays are contiguous AoS exactly as the reference's Vector<Real> holds them:
  *      r_trg[Nt*3] = {x0,y0,z0,x1,...}   r_src[Ns*3]   n_src[Ns*NormalDim]   v_src[Ns*SrcDim]   v_trg[Nt*TrgDim]
  *    n_src may be NULL iff NormalDim == 0 (generic-kernel.txx:97).
- *  - dX = x_trg - x_src (generic-kernel.txx:83); pairs with |dX|^2 == 0 contribute exactly 0
- *    (kernel_functions.hpp:28); the scale factor is applied once after the sum (generic-kernel.txx:184).
+ *  - dX = x_trg - x_src (generic-kernel.txx:83); pairs with |dX|^2 == 0 contribute exactly 0 and every pair with
+ *    |dX|^2 > 0 - subnormal values included - a finite rinv (the r2 > 0 mask of kernel_functions.hpp:28); the scale
+ *    factor is applied once after the sum (generic-kernel.txx:184).
  *  - Every function returns 0 on success or a SCTL_B200_ERR_* code; sctl_b200_last_error() returns a
  *    thread-local message. There is NO CPU fallback: without a usable CUDA device every compute call fails
  *    with SCTL_B200_ERR_CUDA. The reference aborts on bad sizes (generic-kernel.txx:94-97); the C++ shim maps
@@ -178,6 +179,14 @@ SCTL_B200_API int sctl_b200_measure_peak(int dtype, double seconds, double* tflo
 /* Timing of the most recent eval / kernel_matrix issued by this thread through the HOST-pointer entry points:
  * milliseconds spent in (h2d, pack, main kernel, reduce, d2h), measured with CUDA events. */
 SCTL_B200_API int sctl_b200_last_timing(double ms[5]);
+
+/* Test hooks (tests/test_gpu_rsqrt.py). sctl_b200_newton_level: the rsqrt refinement level (0 seed, 1 one Newton step, 2 full
+ * precision) the kernels use for `digits`; -1 for a bad dtype. No GPU needed. sctl_b200_test_rsqrt: y[i] = the device rsqrt of
+ * that level applied to x[i] (HOST pointers), mode 1 = the masked form of the one-launch / KernelMatrix kernels and of
+ * repaired tiles (x > 0 ? 1/sqrt(x) : 0, approx_rsqrt<digits>(x, x > 0) of vec.txx:361-364), mode 0 / 2 = the unmasked form
+ * of the tiled hot loop with an arbitrary / worst-case low word in the seed (x <= 0 or subnormal gives inf or NaN there). */
+SCTL_B200_API int sctl_b200_newton_level(int dtype, int digits);
+SCTL_B200_API int sctl_b200_test_rsqrt(int dtype, int newton, int mode, int64_t n, const void* x, void* y);
 
 SCTL_B200_API const char* sctl_b200_last_error(void);
 SCTL_B200_API const char* sctl_b200_version(void);

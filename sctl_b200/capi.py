@@ -57,6 +57,8 @@ SYMBOLS = {
     "sctl_b200_launch_count": (c_int64, []),
     "sctl_b200_measure_peak": (c_int, [c_int, c_double, POINTER(c_double)]),
     "sctl_b200_last_timing": (c_int, [POINTER(c_double)]),
+    "sctl_b200_newton_level": (c_int, [c_int, c_int]),
+    "sctl_b200_test_rsqrt": (c_int, [c_int, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "sctl_b200_last_error": (c_char_p, []),
     "sctl_b200_version": (c_char_p, []),
 }

@@ -60,13 +60,16 @@ static double kernel_scale(int kid) {
 }
 
 // digits -> rsqrt refinement level (common.cuh). The reference relaxes the Newton count with digits
-// (intrin-wrapper.hpp:3026); we never deliver fewer digits than asked for.
+// (intrin-wrapper.hpp:3026: 14-bit seed for digits <= 4, one iteration = 2^-28 up to 8, two from 9). Here the levels are
+// the bare seed (rel. err <= 2^-19, f32 2^-22), one Newton step (<= 2^-37) and full precision; a level is used only while
+// its error stays below 0.2 * 10^-digits, so that the rinv^3 / rinv^5 kernels still hold `digits` digits
+// (tests/test_gpu_rsqrt.py measures the three bounds on the device and checks this table against them).
 static int newton_level(int dtype, int digits) {
   if (dtype == SCTL_B200_F64) {
-    if (digits < 0 || digits > 12) return 2;
-    return digits > 5 ? 1 : 0;  // the bare MUFU.RSQ64H seed is good to ~2^-19 (5.7 digits)
+    if (digits < 0 || digits > 10) return 2;
+    return digits > 4 ? 1 : 0;
   }
-  return (digits < 0 || digits > 6) ? 1 : 0;
+  return (digits < 0 || digits > 5) ? 1 : 0;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1191,6 +1194,11 @@ int sctl_b200_last_timing(double ms[5]) {
   if (!ms) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
   for (int i = 0; i < 5; i++) ms[i] = t_timing[i];
   return 0;
+}
+
+int sctl_b200_newton_level(int dtype, int digits) {
+  if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return -1;
+  return newton_level(dtype, digits);
 }
 
 const char* sctl_b200_last_error(void) { return t_last_error.c_str(); }

@@ -53,28 +53,37 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
 //   NEWTON 1: one quadratic Newton step       (rel. err ~1.5*2^-44 -> digits <= 12), 3 FP64 ops
 //   NEWTON 2: one cubic (Halley-type) step    (rel. err ~1 ulp),  5 FP64 ops
 //       e = 1 - x*y0^2 ;  y1 = y0 * (1 + e/2 + 3e^2/8)     [1/sqrt(1-e) to second order]
-// The r2 == 0 mask is applied to the SEED with integer ops on the ALU pipe (as the reference masks
-// the seed, intrin-wrapper.hpp:3045), so masked lanes stay exactly 0 through the refinement and the
-// FP64 pipe sees no compare/select. Denormal r2 (< 2^-1022) is treated as 0, as .ftz does.
+// The mask is the reference's: r2 > 0 (kernel_functions.hpp:28) - r2 == 0 gives exactly 0, every positive r2 a finite
+// rinv, SUBNORMAL r2 included (the reference's seed instruction handles denormals, intrin-wrapper.hpp:3038-3049;
+// MUFU.RSQ flushes them, so they are rescaled by an exact power of four first: rsqrt(r2) = 2^k rsqrt(4^k r2)).
+// The test is an integer compare on the high word (ALU pipe), the FP64 pipe sees no compare/select; the rare
+// zero / subnormal case is a branch.
 // ---------------------------------------------------------------------------------------------
 template <int NEWTON>
-__device__ __forceinline__ double rsqrt_masked(double r2) {
+__device__ __forceinline__ double rsqrt_pos_normal(double r2) {  // r2 positive and normal
   double seed;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(seed) : "d"(r2));
-  const bool ok = __double2hiint(r2) >= 0x00100000;  // positive normal number
-  const int hi = ok ? __double2hiint(seed) : 0;
+  const int hi = __double2hiint(seed);
   const double y0 = __hiloint2double(hi, 0);
   if (NEWTON == 0) return y0;
   const double t = r2 * y0;
   const double e = fma(-t, y0, 1.0);
   if (NEWTON == 1) {
-    // y0/2 by an exponent decrement on the integer pipe (y0 is normal or exactly 0 here)
-    const double h = __hiloint2double(ok ? hi - 0x00100000 : 0, 0);
+    // y0/2 by an exponent decrement on the integer pipe (y0 is a positive normal number here)
+    const double h = __hiloint2double(hi - 0x00100000, 0);
     return fma(h, e, y0);
   }
   const double p = fma(e, 0.375, 0.5);
   const double q = e * p;
   return fma(y0, q, y0);
+}
+template <int NEWTON>
+__device__ __forceinline__ double rsqrt_masked(double r2) {
+  if (__double2hiint(r2) < 0x00100000) {  // zero or subnormal (r2 is a sum of squares: never negative)
+    if (!(r2 > 0.0)) return 0.0;          // the r2 > 0 mask: a coincident pair contributes exactly 0
+    return rsqrt_pos_normal<NEWTON>(r2 * 0x1p108) * 0x1p54;
+  }
+  return rsqrt_pos_normal<NEWTON>(r2);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -121,16 +130,22 @@ __device__ __forceinline__ float rsqrt_unmasked(float r2, float) {
 // FP32: MUFU.RSQ (rsqrt.approx.ftz.f32, ~2^-22.4) + one Newton step for full precision, as the
 // reference's 1 iteration at digits = 6 (intrin-wrapper.hpp:3026).
 template <int NEWTON>
-__device__ __forceinline__ float rsqrt_masked(float r2) {
-  float seed;
-  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"(r2));
-  const bool ok = __float_as_int(r2) >= 0x00800000;
-  const float y0 = ok ? seed : 0.0f;
+__device__ __forceinline__ float rsqrt_pos_normal(float r2) {
+  float y0;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y0) : "f"(r2));
   if (NEWTON == 0) return y0;
   const float t = r2 * y0;
   const float e = fmaf(-t, y0, 1.0f);
   const float h = 0.5f * y0;
   return fmaf(h, e, y0);
+}
+template <int NEWTON>
+__device__ __forceinline__ float rsqrt_masked(float r2) {
+  if (__float_as_int(r2) < 0x00800000) {  // zero or subnormal (|dX| < 1.1e-19): same rule as the f64 overload
+    if (!(r2 > 0.0f)) return 0.0f;
+    return rsqrt_pos_normal<NEWTON>(r2 * 0x1p48f) * 0x1p24f;
+  }
+  return rsqrt_pos_normal<NEWTON>(r2);
 }
 
 template <class Real> struct VecOf;

@@ -72,11 +72,17 @@ __global__ void __launch_bounds__(256) pack_kernel(const Real* __restrict__ r_sr
   Real out[REC];
 #pragma unroll
   for (int i = 0; i < REC; i++) out[i] = (Real)0;
+  {
+    // Tail padding repeats the LAST real source's position with a zero payload: the unmasked hot loop then never sees
+    // geometry the caller did not supply (a dummy at the origin would overflow r2 for far-away f32 targets and poison
+    // the tile with inf * 0), and a dummy pair contributes exactly 0 like the reference's absent pair.
+    const long long sc = s < Ns ? s : Ns - 1;
+    out[0] = r_src[sc * 3 + 0];
+    out[1] = r_src[sc * 3 + 1];
+    out[2] = r_src[sc * 3 + 2];
+  }
   if (s < Ns) {
     Real n[3] = {0, 0, 0}, f[Ker::K0];
-    out[0] = r_src[s * 3 + 0];
-    out[1] = r_src[s * 3 + 1];
-    out[2] = r_src[s * 3 + 2];
 #pragma unroll
     for (int i = 0; i < Ker::ND; i++) n[i] = n_src[s * Ker::ND + i];
 #pragma unroll

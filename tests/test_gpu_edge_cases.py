@@ -69,6 +69,53 @@ def test_wide_coordinate_range(checker):
     assert rel_l2(got, want) <= 1e-12
 
 
+@pytest.mark.parametrize("dt,scale,tol", [(np.float32, 1e-20, 1e-3), (np.float64, 1e-158, 1e-5)], ids=["f32-1e-20", "f64-1e-158"])
+def test_subnormal_r2_is_not_masked(reference, dt, scale, tol):
+    """The mask of the reference is r2 > 0 (kernel_functions.hpp:28), not "r2 is a normal number": a point cloud scaled so that
+    every |dX|^2 is SUBNORMAL (f32: |dX| ~ 1e-20, r2 ~ 1e-40 < 1.18e-38; f64: |dX| ~ 1e-158) still interacts - MUFU.RSQ
+    flushes subnormals, so rsqrt_masked rescales them, and the unmasked hot loop repairs the tile. Checked against the
+    closed form in extended precision (tolerance = the precision a subnormal r2 still carries) and, on an AVX-512 host (whose
+    seed instruction handles denormals, intrin-wrapper.hpp:3038-3049), against the reference itself at digits = 4 - the
+    seed-only level: with Newton steps the reference squares the seed (y*y, intrin-wrapper.hpp:519-528), which overflows
+    for r2 this small and turns its own result into -inf, so only its unrefined form can be compared. Laplace FxU only:
+    rinv^2 of such a pair overflows in every other kernel, in the reference too."""
+    kid = 0
+    d = capi.kernel_dims(kid)
+    Nt, Ns = 70, 300
+    Xt, Xs, _, F = synth.make_problem(d, Nt, Ns, np.float64, coincident=5)
+    Xt, Xs, F = (Xt * scale).astype(dt), (Xs * scale).astype(dt), F.astype(dt)
+    dX = Xt.astype(np.longdouble).reshape(-1, 1, 3) - Xs.astype(np.longdouble).reshape(1, -1, 3)
+    r2 = (dX**2).sum(-1)
+    assert 0 < float(np.max(r2)) < np.finfo(dt).tiny and np.count_nonzero(r2 == 0) == 5
+    rinv = np.where(r2 > 0, 1 / np.sqrt(np.where(r2 > 0, r2, 1)), 0)
+    want = np.asarray((rinv * F.astype(np.longdouble).reshape(1, Ns)).sum(1) / (4 * np.pi), dtype=np.float64)
+    for digits in (-1, 8, 3):
+        got = KERNELS[kid]().Eval(None, Xt, Xs, None, F, digits=digits)
+        assert np.all(np.isfinite(got)) and np.all(got != 0)
+        assert rel_l2(got, want) <= max(tol, 10.0**-digits if digits > 0 else 0)
+    if "avx512" in reference.path:
+        ref = reference.eval(kid, Xt, Xs, None, F, digits=4)
+        assert np.all(np.isfinite(ref))
+        assert rel_l2(KERNELS[kid]().Eval(None, Xt, Xs, None, F), ref) <= tol + 2e-4  # 14-bit seed of the reference
+
+
+@pytest.mark.parametrize("Ns", [300, 256, 1, 2049])
+def test_far_from_origin_f32_with_ragged_source_tile(checker, Ns):
+    """f32 coordinates beyond sqrt(FLT_MAX) = 1.8e19 with a source count that is not a multiple of the 256-source tile: the tile
+    padding must not invent geometry (a dummy source at the origin would overflow r2 and poison the tile with inf * 0)."""
+    kid, dt = 0, np.float32
+    d = capi.kernel_dims(kid)
+    Xt, Xs, _, F = synth.make_problem(d, 500, Ns, np.float64, coincident=0)
+    Xt, Xs = (3.0e19 + Xt * 1e16).astype(dt), (3.0e19 + Xs * 1e16).astype(dt)
+    Xt[:3] = Xs[-3:]  # one target sits on the LAST source, the one the padding repeats
+    F = F.astype(dt)
+    f64 = lambda a: a.astype(np.float64)
+    want = checker.eval(kid, f64(Xt), f64(Xs), None, f64(F))
+    got = KERNELS[kid]().Eval(None, Xt, Xs, None, F)
+    assert np.all(np.isfinite(got))
+    assert rel_l2(got, want) <= 1e-5
+
+
 def test_non_finite_inputs_do_not_hang_or_spread():
     """a NaN density or an Inf coordinate poisons every target it interacts with (as the reference's arithmetic does); the call
     returns, and later calls are unaffected (no sticky device error, no stale workspace)"""

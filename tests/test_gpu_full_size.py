@@ -42,6 +42,57 @@ def _subset_check(checker, kid, Xt, Xs, Xn, F, U, tol, seed=7):
     return err
 
 
+def test_c1_full_compare(checker):
+    """C1 = BASELINE.json configs[0]: Laplace3D_FxU f64, 20 000 sources x 20 000 targets, the reference's own CPU-runnable
+    case. SURVEY 8(c): "C1 is compared in full" - ALL 20 000 targets against the reference's Eval<double,true>
+    (generic-kernel.txx:76-189), through the host-pointer entry (what the C++ shim calls), the device-pointer entry, the
+    accumulate form, and at N+3 (ragged tails). 20k a side is also the size where the launch planner switches between its
+    variants, so every planner choice that is reachable by environment knob is pinned against the same oracle."""
+    import torch
+
+    kid, N = 0, 20_000
+    d = capi.kernel_dims(kid)
+    ker = KERNELS[kid]()
+    worst = {}
+    for n in (N, N + 3):
+        Xt, Xs, Xn, F = synth.make_problem(d, n, n, np.float64)
+        want = checker.eval(kid, Xt, Xs, None, F)
+        assert np.all(np.isfinite(want))
+        got_h = ker.Eval(None, Xt, Xs, None, F)  # host pointers
+        got_d = ker.Eval(None, _dev(Xt), _dev(Xs), None, _dev(F))  # device pointers, torch's stream
+        torch.cuda.synchronize()
+        got_d = got_d.cpu().numpy()
+        for tag, got in (("host", got_h), ("device", got_d)):
+            err = rel_l2(got, want)
+            mx = float(np.max(np.abs(got - want)) / np.max(np.abs(want)))  # worst single target, relative to the largest potential
+            worst[(n, tag)] = (err, mx)
+            assert np.all(np.isfinite(got))
+            assert err <= TOL[np.dtype(np.float64)], f"C1 {tag} n={n}: rel-L2 {err:.3e}"
+            assert mx <= 1e-12, f"C1 {tag} n={n}: max error / max|U| {mx:.3e}"  # no single target is off
+        np.testing.assert_array_equal(got_h, got_d)  # same kernels, fixed reduction order: bit-identical
+        # accumulate into a sized v_trg (generic-kernel.txx:98-101)
+        acc = np.full(n, 0.25)
+        acc = ker.Eval(acc, Xt, Xs, None, F)
+        assert rel_l2(acc - 0.25, want) <= 1e-12
+    print("C1 full compare (rel-L2, max-rel):", worst)
+
+
+@pytest.mark.parametrize("knobs", [{"SCTL_B200_RBIG_MIN_CTAS_PER_SM": "1000000"}, {"SCTL_B200_RBIG_MIN_CTAS_PER_SM": "0"},
+                                   {"SCTL_B200_FORCE_CHUNKS": "1"}, {"SCTL_B200_FORCE_CHUNKS": "79"}, {"SCTL_B200_WQ": "1"}, {"SCTL_B200_WQ": "0"}],
+                         ids=["R1", "Rbig", "1chunk", "79chunks", "workqueue", "grid"])
+def test_c1_every_planner_variant(checker, monkeypatch, knobs):
+    """C1 again with the launch planner pinned to each of its variants (R = 1 / register-blocked, unsplit / split source range,
+    work-queue / plain grid): the planner's choice must never change the answer beyond summation order."""
+    kid, N = 0, 20_000
+    for k, v in knobs.items():
+        monkeypatch.setenv(k, v)
+    d = capi.kernel_dims(kid)
+    Xt, Xs, Xn, F = synth.make_problem(d, N, N, np.float64)
+    want = checker.eval(kid, Xt, Xs, None, F)
+    got = KERNELS[kid]().Eval(None, _dev(Xt), _dev(Xs), None, _dev(F)).cpu().numpy()
+    assert rel_l2(got, want) <= TOL[np.dtype(np.float64)]
+
+
 @pytest.mark.parametrize("kid,N,dt", [(0, 1_000_000, np.float64), (2, 1_000_000, np.float64),  # C2
                                       (3, 4_000_000, np.float64),                              # C3
                                       (1, 2_000_000, np.float64), (4, 2_000_000, np.float64)], # C4

@@ -64,7 +64,8 @@ enum { SCTL_B200_F32 = 0, SCTL_B200_F64 = 1 };
 enum {
   SCTL_B200_DEVICE_PTRS = 1u << 0, /* all pointers are device pointers on the current CUDA device */
   SCTL_B200_OVERWRITE = 1u << 1,   /* v_trg = scale*sum instead of v_trg += scale*sum (EvalDirect zeroes U first, fmm-wrapper.txx:501-502) */
-  SCTL_B200_ALL_GPUS = 1u << 2     /* host pointers only: shard targets over every visible GPU of this process (fmm-wrapper.txx:504-510 analogue) */
+  SCTL_B200_ALL_GPUS = 1u << 2     /* host pointers only: shard targets over every visible GPU of this process (fmm-wrapper.txx:504-510 analogue);
+                                      each GPU uploads 1/G of the sources and NCCL replicates them over NVLink */
 };
 
 /* error codes */
@@ -74,7 +75,8 @@ enum {
   SCTL_B200_ERR_DTYPE = 2,  /* unknown dtype */
   SCTL_B200_ERR_ARG = 3,    /* null pointer / negative size / bad flag combination */
   SCTL_B200_ERR_CUDA = 4,   /* CUDA runtime error or no usable device (no CPU fallback) */
-  SCTL_B200_ERR_NOMEM = 5   /* device allocation failed */
+  SCTL_B200_ERR_NOMEM = 5,  /* device allocation failed */
+  SCTL_B200_ERR_NCCL = 6    /* NCCL could not be loaded, or an NCCL call failed */
 };
 
 /* Metadata — replaces CoordDim()/NormalDim()/SrcDim()/TrgDim() (generic-kernel.txx:22-36),
@@ -168,6 +170,48 @@ SCTL_B200_API int sctl_b200_sm_count(int* n);
  * staging blocks and forgets the selection. Both are optional: every entry point initialises lazily. */
 SCTL_B200_API int sctl_b200_init(int ndev, const int* dev_ids);
 SCTL_B200_API int sctl_b200_finalize(void);
+
+/* NCCL target-sharding driver: one rank per GPU (MPI ranks, torchrun workers, or threads of one process), every rank
+ * holding ITS block of the targets and ITS block of every source array - the multi-rank form of ParticleFMM::EvalDirect
+ * (fmm-wrapper.txx:490-562). The reference sends every source block round an Isend/Irecv ring and evaluates after each
+ * round (:537-558); here the blocks are replicated with one ncclAllGather per source array over NVLink (a group of
+ * ncclBroadcasts when the blocks are ragged) and ONE Eval runs over all sources. Targets never move, so there is no
+ * reduction and results stay with their owner (the reference re-partitions U back, :560-561).
+ *   sctl_b200_partition       [begin, end) of rank's block of n items: the formula of fmm-wrapper.txx:507 (PartitionN).
+ *   sctl_b200_comm_unique_id  rank 0 creates the 128-byte NCCL id and distributes it by any means it has (MPI_Bcast,
+ *                             sctl::Comm::Bcast, torch.distributed, a file); id_bytes >= 128.
+ *   sctl_b200_comm_create     collective over all ranks: ncclCommInitRank on the CURRENT device (call
+ *                             sctl_b200_set_device first). nranks == 1 needs no id and never loads NCCL.
+ *   sctl_b200_eval_sharded    v_trg[Nt_local*K1] (+)= scale * sum over ALL ranks' sources. Collective: every rank of the
+ *                             communicator must call it with the same kernel_id / dtype / digits. Host pointers (default;
+ *                             each rank uploads only its own blocks) or SCTL_B200_DEVICE_PTRS; SCTL_B200_OVERWRITE as for
+ *                             sctl_b200_eval. src_counts: the number of sources of every rank (nranks entries), or NULL
+ *                             to have them exchanged (one 8-byte all-gather and a stream synchronisation per call).
+ *                             Synchronous. A communicator carries one call at a time (not thread-safe per handle).
+ *   ..._async                 device pointers, enqueued on the caller's stream, no synchronisation when src_counts is given.
+ * NCCL is loaded at the first communicator with nranks > 1 (dlopen of libnccl.so.2, or the file SCTL_B200_NCCL_LIB names);
+ * it is not a link-time dependency. An error on one rank before the collective leaves the other ranks waiting in it - the
+ * reference aborts all ranks in that case (SCTL_ASSERT); callers should treat a non-zero return as fatal. */
+SCTL_B200_API int sctl_b200_partition(int64_t n, int rank, int nranks, int64_t* begin, int64_t* end);
+SCTL_B200_API int sctl_b200_comm_unique_id(void* id, int64_t id_bytes);
+SCTL_B200_API int sctl_b200_comm_create(void** comm, int nranks, int rank, const void* nccl_unique_id);
+SCTL_B200_API int sctl_b200_comm_destroy(void* comm);
+SCTL_B200_API int sctl_b200_comm_info(void* comm, int* rank, int* nranks, int* device);
+SCTL_B200_API int sctl_b200_nccl_version(int* version);
+SCTL_B200_API int sctl_b200_eval_sharded(void* comm, int kernel_id, int dtype, int64_t Nt_local, int64_t Ns_local, const void* r_trg,
+                           const void* r_src, const void* n_src, const void* v_src, void* v_trg, int digits, unsigned flags,
+                           const int64_t* src_counts);
+SCTL_B200_API int sctl_b200_eval_sharded_async(void* comm, int kernel_id, int dtype, int64_t Nt_local, int64_t Ns_local, const void* d_r_trg,
+                                 const void* d_r_src, const void* d_n_src, const void* d_v_src, void* d_v_trg, int digits, unsigned flags,
+                                 const int64_t* src_counts, void* cuda_stream);
+/* Multi-rank particle registry: after sctl_b200_fmm_set_comm every rank hands ITS particles to the Set* calls (which become
+ * collective): sources are all-gathered when they are SET, not on every evaluation as the reference's ring does
+ * (fmm-wrapper.txx:537-558) - a solver that sets coordinates once and a new density per iteration moves 8*SrcDim bytes per
+ * source per iteration and every eval_direct is a local launch sequence. Targets stay with their owner unless the ranks hold
+ * uneven numbers (more than 5 % above the mean): then they are re-partitioned by the reference's formula (:504-510) with one
+ * all-gather of coordinates at SetTrgCoord and one of the potentials per eval_direct (:560-561). eval_direct returns the
+ * potentials of the rank's OWN targets in both cases. comm == NULL detaches. The communicator must outlive the registry. */
+SCTL_B200_API int sctl_b200_fmm_set_comm(void* fmm, void* comm);
 
 /* Measurement helpers (bench.py): number of kernel launches this library has issued from this process, and a
  * register-resident DFMA / FFMA chain that measures the CUDA-core FP64 / FP32 peak used as roofline

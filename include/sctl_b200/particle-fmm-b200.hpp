@@ -10,9 +10,13 @@
 // Differences: (1) coordinates, normals, densities and packed source records stay in HBM between calls — a GMRES loop
 // that only calls SetSrcDensity + Eval re-uploads just the density; (2) Eval == EvalDirect, exactly like a reference
 // build without PVFMM (fmm-wrapper.txx:481-489): the FMM far field is an external dependency of the reference and not
-// part of this library; SetKernels / the M2M..L2T kernels are accepted and dimension-checked only; (3) single rank: the
-// MPI ring of EvalDirect (fmm-wrapper.txx:537-558) is replaced by the NCCL driver of sctl_b200/distributed.py for
-// one-process-per-GPU runs. Only the eight kernel_impl micro-kernels are supported as S2T kernels.
+// part of this library; SetKernels / the M2M..L2T kernels are accepted and dimension-checked only; (3) multi-rank: the
+// MPI ring of EvalDirect (fmm-wrapper.txx:537-558) is replaced by the NCCL driver inside libsctl_b200.so. With a
+// sctl::Comm of Size() > 1 (an MPI build of SCTL, one rank per GPU, sctl_b200_set_device(local_rank) called first) the
+// constructor / SetComm bootstrap an NCCL communicator through the reference's own Comm::Bcast (comm.hpp:167); programs
+// that bring their own ranks (threads, another launcher) pass a handle from sctl_b200_comm_create to SetComm(void*).
+// Every rank then hands ITS particles to the Set* calls (collective) and Eval returns the potentials of its own targets,
+// exactly the reference's calling convention. Only the eight kernel_impl micro-kernels are supported as S2T kernels.
 #ifndef SCTL_B200_PARTICLE_FMM_B200_HPP_
 #define SCTL_B200_PARTICLE_FMM_B200_HPP_
 
@@ -33,13 +37,31 @@ template <class Real, sctl::Integer DIM = 3> class ParticleFMM {
   ParticleFMM(const ParticleFMM&) = delete;
   ParticleFMM& operator=(const ParticleFMM&) = delete;
 
-  ParticleFMM(const sctl::Comm& comm = sctl::Comm::Self()) : h_(nullptr) {
-    SCTL_ASSERT_MSG(comm.Size() == 1, "sctl_b200::ParticleFMM is single-rank; use the NCCL driver for multi-GPU runs.");
+  ParticleFMM(const sctl::Comm& comm = sctl::Comm::Self()) : h_(nullptr), owned_comm_(nullptr) {
     sctl_b200_shim::check(sctl_b200_fmm_create(&h_, sctl_b200_shim::DType<Real>::value), "sctl_b200_fmm_create");
+    SetComm(comm);
   }
-  ~ParticleFMM() { sctl_b200_fmm_destroy(h_); }
+  ~ParticleFMM() {
+    sctl_b200_fmm_destroy(h_);
+    sctl_b200_comm_destroy(owned_comm_);
+  }
 
-  void SetComm(const sctl::Comm& comm) { SCTL_ASSERT_MSG(comm.Size() == 1, "sctl_b200::ParticleFMM is single-rank."); }
+  // fmm-wrapper.txx:204 / fmm-wrapper.hpp:45. Collective over `comm` when comm.Size() > 1: rank 0 creates the NCCL id, the
+  // reference's Comm::Bcast carries it, every rank joins on its current CUDA device.
+  void SetComm(const sctl::Comm& comm) {
+    sctl_b200_shim::check(sctl_b200_fmm_set_comm(h_, nullptr), "sctl_b200_fmm_set_comm");
+    sctl_b200_comm_destroy(owned_comm_);
+    owned_comm_ = nullptr;
+    if (comm.Size() == 1) return;
+    sctl::Vector<char> id(128);
+    id.SetZero();
+    if (comm.Rank() == 0) sctl_b200_shim::check(sctl_b200_comm_unique_id(&id[0], 128), "sctl_b200_comm_unique_id");
+    comm.Bcast(id.begin(), 128, 0);
+    sctl_b200_shim::check(sctl_b200_comm_create(&owned_comm_, (int)comm.Size(), (int)comm.Rank(), &id[0]), "sctl_b200_comm_create");
+    sctl_b200_shim::check(sctl_b200_fmm_set_comm(h_, owned_comm_), "sctl_b200_fmm_set_comm");
+  }
+  // a communicator the caller created with sctl_b200_comm_create (not owned; nullptr detaches)
+  void SetComm(void* sctl_b200_comm) { sctl_b200_shim::check(sctl_b200_fmm_set_comm(h_, sctl_b200_comm), "sctl_b200_fmm_set_comm"); }
   void SetAccuracy(sctl::Integer digits) { sctl_b200_shim::check(sctl_b200_fmm_set_accuracy(h_, (int)digits), "sctl_b200_fmm_set_accuracy"); }
 
   template <class KerM2M, class KerM2L, class KerL2L> void SetKernels(const KerM2M& ker_m2m, const KerM2L& ker_m2l, const KerL2L& ker_l2l) {
@@ -70,6 +92,7 @@ template <class Real, sctl::Integer DIM = 3> class ParticleFMM {
   void SetSrcCoord(const std::string& name, const sctl::Vector<Real>& src_coord, const sctl::Vector<Real>& src_normal = sctl::Vector<Real>()) {
     const sctl::Long Ns = src_coord.Dim() / DIM;
     SCTL_ASSERT(src_coord.Dim() == Ns * DIM);
+    SCTL_ASSERT(src_normal.Dim() == 0 || src_normal.Dim() == Ns * DIM);  // the C ABI reads Ns*NormalDim values (fmm-wrapper.txx:535)
     sctl_b200_shim::check(sctl_b200_fmm_set_src_coord(h_, name.c_str(), (int64_t)Ns, sctl_b200_shim::cptr(src_coord), sctl_b200_shim::cptr(src_normal), 0u),
                           "sctl_b200_fmm_set_src_coord");
   }
@@ -105,6 +128,7 @@ template <class Real, sctl::Integer DIM = 3> class ParticleFMM {
 
  private:
   void* h_;
+  void* owned_comm_;
 };
 
 }  // namespace sctl_b200

@@ -47,7 +47,7 @@ for it in range(3):  # density updates, as in a solver loop
     want = dl.Eval(want, T(Xt[3 * t0:3 * t1]), T(Xs), T(Xn), T((it + 1.0) * F))
     err = float(torch.linalg.norm(U - want) / torch.linalg.norm(want))
     ok = ok and err < 1e-12 and U.numel() == 3 * (t1 - t0)
-    print(f"rank {rank} it {it}: own targets {t1 - t0}, evaluated block {fmm._trg['U']['hi'] - fmm._trg['U']['lo']}, moved={fmm._trg['U']['moved']}, eval {e0.elapsed_time(e1):.2f} ms, rel-L2 vs single-GPU {err:.2e}", flush=True)
+    print(f"rank {rank} it {it}: own targets {t1 - t0} of {N} (skewed: re-partitioned inside libsctl_b200.so), eval {e0.elapsed_time(e1):.2f} ms, rel-L2 vs single-GPU {err:.2e}", flush=True)
 print(f"rank {rank}: {'OK' if ok else 'FAIL'}", flush=True)
 dist.barrier()
 dist.destroy_process_group()

@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("SCTL_B200_LIB") or os.path.join(os.path.dirname(os.pa
 # enums of include/sctl_b200.h
 F32, F64 = 0, 1
 DEVICE_PTRS, OVERWRITE, ALL_GPUS = 1, 2, 4
-ERR_KERNEL, ERR_DTYPE, ERR_ARG, ERR_CUDA, ERR_NOMEM = 1, 2, 3, 4, 5
+ERR_KERNEL, ERR_DTYPE, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_NCCL = 1, 2, 3, 4, 5, 6
 
 # every symbol include/sctl_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
@@ -54,6 +54,17 @@ SYMBOLS = {
     "sctl_b200_finalize": (c_int, []),
     "sctl_b200_get_device": (c_int, [POINTER(c_int)]),
     "sctl_b200_sm_count": (c_int, [POINTER(c_int)]),
+    "sctl_b200_partition": (c_int, [c_int64, c_int, c_int, POINTER(c_int64), POINTER(c_int64)]),
+    "sctl_b200_comm_unique_id": (c_int, [c_void_p, c_int64]),
+    "sctl_b200_comm_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_void_p]),
+    "sctl_b200_comm_destroy": (c_int, [c_void_p]),
+    "sctl_b200_comm_info": (c_int, [c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "sctl_b200_nccl_version": (c_int, [POINTER(c_int)]),
+    "sctl_b200_eval_sharded": (c_int, [c_void_p, c_int, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_uint,
+                                       POINTER(c_int64)]),
+    "sctl_b200_eval_sharded_async": (c_int, [c_void_p, c_int, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_uint,
+                                             POINTER(c_int64), c_void_p]),
+    "sctl_b200_fmm_set_comm": (c_int, [c_void_p, c_void_p]),
     "sctl_b200_launch_count": (c_int64, []),
     "sctl_b200_measure_peak": (c_int, [c_int, c_double, POINTER(c_double)]),
     "sctl_b200_last_timing": (c_int, [POINTER(c_double)]),

@@ -3,6 +3,7 @@
 // in-process multi-GPU target sharding. No CPU fallback anywhere: a missing device is an error.
 #include <atomic>
 #include <cmath>
+#include <deque>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -13,6 +14,7 @@
 #include <vector>
 
 #include "../../include/sctl_b200.h"
+#include "internal.h"
 #include "launch.h"
 
 namespace sctl_b200 {
@@ -26,7 +28,7 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 static thread_local std::string t_last_error;
 static thread_local double t_timing[5] = {0, 0, 0, 0, 0};
 
-static int set_error(int code, const char* fmt, ...) {
+int set_error(int code, const char* fmt, ...) {
   char buf[512];
   va_list ap;
   va_start(ap, fmt);
@@ -35,26 +37,18 @@ static int set_error(int code, const char* fmt, ...) {
   t_last_error = buf;
   return code;
 }
-static int cuda_error(cudaError_t e, const char* what) {
+int cuda_error(cudaError_t e, const char* what) {
   return set_error(SCTL_B200_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
 }
-#define CU_TRY(call)                                       \
-  do {                                                     \
-    cudaError_t e__ = (call);                              \
-    if (e__ != cudaSuccess) return cuda_error(e__, #call); \
-  } while (0)
+const char* last_error_cstr() { return t_last_error.c_str(); }
 
-struct KernelInfo {
-  const char* name;
-  int normal_dim, src_dim, trg_dim, flops;
-  double scale_num, scale_den_pi;
-};
 // kernel_functions.hpp:15-198 (Name, FLOPS, uKerScaleFactor) and the dims deduced by generic-kernel.hpp:33-52
 static const KernelInfo KINFO[NUM_KERNELS] = {
     {"Laplace3D-FxU", 0, 1, 1, 6, 1.0, 4.0},    {"Laplace3D-DxU", 3, 1, 1, 14, 1.0, 4.0}, {"Laplace3D-FxdU", 0, 1, 3, 11, -1.0, 4.0},
     {"Stokes3D-FxU", 0, 3, 3, 23, 1.0, 8.0},    {"Stokes3D-DxU", 3, 3, 3, 26, 3.0, 4.0},  {"Stokes3D-FxT", 0, 3, 9, 39, -3.0, 4.0},
     {"Stokes3D-FSxU", 0, 4, 3, 26, 1.0, 8.0},   {"Stokes3D-FxUP", 0, 3, 4, 26, 1.0, 8.0},
 };
+const KernelInfo& kernel_info(int kernel_id) { return KINFO[kernel_id]; }
 static double kernel_scale(int kid) {
   return (double)((long double)KINFO[kid].scale_num / ((long double)KINFO[kid].scale_den_pi * 3.14159265358979323846264338327950288L));
 }
@@ -75,24 +69,22 @@ static int newton_level(int dtype, int digits) {
 // ------------------------------------------------------------------------------------------------
 // per-thread, per-device context: one non-blocking stream + timing events
 // ------------------------------------------------------------------------------------------------
-struct DevCtx {
-  int dev = -1;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  int sms = 0;
-  // staging pair for small host-pointer calls (allocated on first use, kept for the thread's lifetime): pinned host
-  // block + device block, so that a call is ONE H2D copy, the kernels, ONE D2H copy and one synchronisation
-  void* h_stage = nullptr;
-  void* d_stage = nullptr;
-};
 constexpr size_t STAGE_BYTES = 1u << 20;
-static thread_local std::vector<DevCtx> t_ctx;
+// The calling thread's contexts, one per device it has used. A deque: push_back never relocates existing elements, so a
+// DevCtx* handed out by get_ctx stays valid when the thread later touches another device. The holder's destructor releases
+// streams, events and staging blocks when the thread exits (long-lived threads may also call sctl_b200_finalize).
+struct ThreadCtxHolder {
+  std::deque<DevCtx> v;
+  ~ThreadCtxHolder();
+};
+static thread_local ThreadCtxHolder t_holder;
+#define t_ctx (t_holder.v)
 static std::mutex g_devices_mutex;
 static std::vector<int> g_devices;  // devices SCTL_B200_ALL_GPUS shards over (sctl_b200_init); empty = every visible device
 static std::mutex g_pool_mutex;
 static std::vector<int> g_pool_configured;
 
-static int get_ctx(DevCtx** out) {
+int get_ctx(DevCtx** out) {
   int dev = 0;
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -133,7 +125,9 @@ static int get_ctx(DevCtx** out) {
 
 // Releases the calling thread's streams, events and staging blocks. Long-lived caller threads (the main thread, an OpenMP
 // team) keep theirs for the life of the process; the short-lived workers of eval_host_all_gpus call this before they exit.
-static void release_thread_ctx() {
+void release_thread_ctx() {
+  if (t_ctx.empty()) return;
+  DeviceGuard guard;
   for (auto& c : t_ctx) {
     if (cudaSetDevice(c.dev) != cudaSuccess) continue;
     if (c.stream) cudaStreamDestroy(c.stream);
@@ -145,33 +139,41 @@ static void release_thread_ctx() {
   t_ctx.clear();
   cudaGetLastError();
 }
+ThreadCtxHolder::~ThreadCtxHolder() { release_thread_ctx(); }
 
-static size_t elem_size(int dtype) { return dtype == SCTL_B200_F64 ? 8 : 4; }
+size_t elem_size(int dtype) { return dtype == SCTL_B200_F64 ? 8 : 4; }
 
-static int check_common(int kernel_id, int dtype, int64_t Nt, int64_t Ns) {
+int check_common(int kernel_id, int dtype, int64_t Nt, int64_t Ns) {
   if (kernel_id < 0 || kernel_id >= NUM_KERNELS) return set_error(SCTL_B200_ERR_KERNEL, "unknown kernel id %d", kernel_id);
   if (dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) return set_error(SCTL_B200_ERR_DTYPE, "unknown dtype %d", dtype);
   if (Nt < 0 || Ns < 0) return set_error(SCTL_B200_ERR_ARG, "negative size Nt=%lld Ns=%lld", (long long)Nt, (long long)Ns);
   return 0;
 }
 
-struct DevAlloc {  // stream-ordered allocation, freed on the same stream
-  void* p = nullptr;
-  cudaStream_t st = nullptr;
-  ~DevAlloc() {
-    if (p) cudaFreeAsync(p, st);
+int DevAlloc::alloc(size_t bytes, cudaStream_t s) {
+  st = s;
+  cudaError_t e = cudaMallocAsync(&p, bytes ? bytes : 16, s);
+  if (e != cudaSuccess) {
+    p = nullptr;
+    cudaGetLastError();
+    return set_error(SCTL_B200_ERR_NOMEM, "cudaMallocAsync(%zu bytes): %s", bytes, cudaGetErrorString(e));
   }
-  int alloc(size_t bytes, cudaStream_t s) {
-    st = s;
-    cudaError_t e = cudaMallocAsync(&p, bytes ? bytes : 16, s);
-    if (e != cudaSuccess) {
-      p = nullptr;
-      cudaGetLastError();
-      return set_error(SCTL_B200_ERR_NOMEM, "cudaMallocAsync(%zu bytes): %s", bytes, cudaGetErrorString(e));
-    }
-    return 0;
+  return 0;
+}
+int DevBuf::reserve(size_t bytes) {
+  if (bytes <= cap) return 0;
+  if (p) cudaFree(p);
+  p = nullptr;
+  cap = 0;
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    p = nullptr;
+    return set_error(SCTL_B200_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", bytes, cudaGetErrorString(e));
   }
-};
+  cap = bytes;
+  return 0;
+}
 
 // ------------------------------------------------------------------------------------------------
 // launch plan for Eval on device-resident AoS arrays
@@ -271,8 +273,8 @@ static bool use_small_path(int64_t Nt, int64_t Ns) {
 }
 
 // pack + eval (+ reduce). ev (optional): 4 events recorded around pack | eval | reduce.
-static int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
-                       const void* v_src, void* v_trg, int digits, bool accumulate, cudaStream_t st, int sms, cudaEvent_t* ev) {
+int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src, const void* v_src,
+                void* v_trg, int digits, bool accumulate, cudaStream_t st, int sms, cudaEvent_t* ev) {
   const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
   const size_t esz = elem_size(dtype);
   if (Nt == 0) return 0;
@@ -449,6 +451,18 @@ static int eval_host_all_gpus(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
   }
   const KernelInfo& ki = KINFO[kernel_id];
   const size_t esz = elem_size(dtype);
+  // Sources: every GPU uploads only ITS 1/G block of the caller's arrays and the blocks are replicated over NVLink by the NCCL
+  // driver of comm.cu (ncclCommInitAll communicators, one per device, cached for the life of the process) - the caller's pageable
+  // memory crosses PCIe once instead of G times. SCTL_B200_ALL_GPUS_MODE=replicate (or a process without NCCL) keeps the
+  // collective-free form: G independent uploads of all sources.
+  static std::mutex all_gpus_mutex;  // the communicators carry one collective sequence at a time
+  std::lock_guard<std::mutex> all_lk(all_gpus_mutex);
+  std::vector<Comm*> comms;
+  const char* mode = getenv("SCTL_B200_ALL_GPUS_MODE");
+  const bool want_nccl = !(mode && !strcmp(mode, "replicate")) && Ns >= ndev;
+  if (want_nccl && comm_all_gpus(devs, comms) != 0) comms.clear();  // NCCL unavailable: replicate
+  std::vector<int64_t> counts(ndev);
+  for (int g = 0; g < ndev; g++) counts[g] = Ns * (g + 1) / ndev - Ns * g / ndev;
   std::vector<int> rcs(ndev, 0);
   std::vector<std::string> msgs(ndev);
   std::vector<std::thread> th;
@@ -460,8 +474,20 @@ static int eval_host_all_gpus(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
         return;
       }
       const int64_t t0 = Nt * g / ndev, t1 = Nt * (g + 1) / ndev;
-      rcs[g] = eval_host_one_device(kernel_id, dtype, t1 - t0, Ns, (const char*)r_trg + (size_t)t0 * 3 * esz, r_src, n_src, v_src,
-                                    (char*)v_trg + (size_t)t0 * ki.trg_dim * esz, digits, accumulate);
+      const char* xt = (const char*)r_trg + (size_t)t0 * 3 * esz;
+      char* ut = (char*)v_trg + (size_t)t0 * ki.trg_dim * esz;
+      if (!comms.empty()) {
+        const int64_t s0 = Ns * g / ndev;
+        DevCtx* c = nullptr;
+        rcs[g] = get_ctx(&c);
+        if (!rcs[g])
+          rcs[g] = eval_sharded_impl(comms[g], kernel_id, dtype, t1 - t0, counts[g], xt, (const char*)r_src + (size_t)s0 * 3 * esz,
+                                     ki.normal_dim ? (const char*)n_src + (size_t)s0 * ki.normal_dim * esz : nullptr,
+                                     (const char*)v_src + (size_t)s0 * ki.src_dim * esz, ut, digits, accumulate ? 0u : (unsigned)SCTL_B200_OVERWRITE,
+                                     counts.data(), c->stream, true);
+      } else {
+        rcs[g] = eval_host_one_device(kernel_id, dtype, t1 - t0, Ns, xt, r_src, n_src, v_src, ut, digits, accumulate);
+      }
       if (rcs[g]) msgs[g] = t_last_error;
       release_thread_ctx();
     });
@@ -602,27 +628,6 @@ static int kmat_batch_impl(int kernel_id, int dtype, int64_t nbatch, const int64
 // the density of that source changed (coordinates are set once, the density changes every solver
 // iteration: boundary_integral.txx:777-778 vs :1054).
 // ------------------------------------------------------------------------------------------------
-struct DevBuf {
-  void* p = nullptr;
-  size_t cap = 0;
-  ~DevBuf() {
-    if (p) cudaFree(p);
-  }
-  int reserve(size_t bytes) {
-    if (bytes <= cap) return 0;
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-    cudaError_t e = cudaMalloc(&p, bytes);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      p = nullptr;
-      return set_error(SCTL_B200_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", bytes, cudaGetErrorString(e));
-    }
-    cap = bytes;
-    return 0;
-  }
-};
 struct FmmSrc {
   int src_dim = 0, normal_dim = 0;
   int64_t Ns = 0;    // from the coordinates
@@ -630,12 +635,19 @@ struct FmmSrc {
   DevBuf X, Xn, F, W;
   int64_t n_wts = 0;  // 0 = no quadrature weights, else must equal Ns
   unsigned long long version = 0;  // bumped by SetSrcCoord / SetSrcDensity / SetSrcWeights
+  std::vector<int64_t> counts;     // multi-rank: sources held by every rank (Ns is their sum); empty until SetSrcCoord
 };
 struct FmmTrg {
   int trg_dim = 0;
-  int64_t Nt = 0;
-  int64_t n_nrm = 0;  // 0 = no target-normal contraction, else must equal Nt*3
+  int64_t Nt = 0;      // targets this rank EVALUATES (its own, or its block of the re-partitioned set)
+  int64_t Nt_own = 0;  // targets this rank handed in = rows eval_direct returns
+  int64_t n_nrm = 0;   // 0 = no target-normal contraction, else must equal Nt*3
   DevBuf X, U, Xn, Ufull;
+  // multi-rank: targets per rank; moved = re-partitioned evenly (fmm-wrapper.txx:504-510) because the ranks hold uneven numbers
+  std::vector<int64_t> counts;
+  bool moved = false;
+  int64_t lo = 0, hi = 0;  // the evaluated block within the concatenated target set
+  DevBuf Ublk, Ugath;
 };
 struct FmmS2T {
   int kernel_id = -1;
@@ -646,6 +658,7 @@ struct FmmCtx {
   int dtype = SCTL_B200_F64;
   int dev = 0;
   int digits = -1;  // ParticleFMM default digits_ = 10 is an FMM tolerance; the direct sum is evaluated at SetAccuracy's value
+  Comm* comm = nullptr;  // multi-rank registry (sctl_b200_fmm_set_comm); not owned
   std::mutex mu;
   std::vector<std::pair<std::string, FmmSrc*>> src;
   std::vector<std::pair<std::string, FmmTrg*>> trg;
@@ -667,6 +680,35 @@ struct FmmCtx {
   }
 };
 
+static bool fmm_multi(const FmmCtx* C) { return C->comm && comm_size(C->comm) > 1; }
+
+// Multi-rank Set*: this rank's block (host or device pointer, counts[rank] particles of `width` bytes) -> replica of all
+// ranks' blocks in `b`. `slice` (optional): keep only particles [lo, hi) of the replica (re-partitioned targets).
+static int fmm_gather(FmmCtx* C, DevBuf& b, const void* src, size_t width, const std::vector<int64_t>& counts, bool device_ptrs, cudaStream_t st,
+                      bool slice = false, int64_t lo = 0, int64_t hi = 0) {
+  const int rank = comm_rank(C->comm);
+  int64_t total = 0;
+  for (int64_t v : counts) total += v;
+  const size_t mine = (size_t)counts[(size_t)rank] * width;
+  DevAlloc tmp, all;
+  const void* d_local = src;
+  int rc;
+  if (!device_ptrs) {
+    if ((rc = tmp.alloc(mine, st))) return rc;
+    if (mine) CU_TRY(cudaMemcpyAsync(tmp.p, src, mine, cudaMemcpyHostToDevice, st));
+    d_local = tmp.p;
+  }
+  if (!slice) {
+    if ((rc = b.reserve((size_t)total * width + 16))) return rc;
+    return comm_allgatherv(C->comm, d_local, width, counts, b.p, st);
+  }
+  if ((rc = all.alloc((size_t)total * width, st))) return rc;
+  if ((rc = comm_allgatherv(C->comm, d_local, width, counts, all.p, st))) return rc;
+  if ((rc = b.reserve((size_t)(hi - lo) * width + 16))) return rc;
+  if (hi > lo) CU_TRY(cudaMemcpyAsync(b.p, (const char*)all.p + (size_t)lo * width, (size_t)(hi - lo) * width, cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
 static int fmm_upload(DevBuf& b, const void* src, size_t bytes, bool device_ptrs, cudaStream_t st) {
   int rc = b.reserve(bytes ? bytes : 16);
   if (rc) return rc;
@@ -682,6 +724,7 @@ using namespace sctl_b200;
   if (!(h)) return set_error(SCTL_B200_ERR_ARG, "null context");                           \
   FmmCtx* C = (FmmCtx*)(h);                                                                \
   std::lock_guard<std::mutex> lk__(C->mu);                                                 \
+  DeviceGuard guard__; /* the caller's current device is restored on return */             \
   CU_TRY(cudaSetDevice(C->dev));                                                           \
   DevCtx* c = nullptr;                                                                     \
   {                                                                                        \
@@ -706,9 +749,19 @@ int sctl_b200_fmm_create(void** fmm, int dtype) {
 int sctl_b200_fmm_destroy(void* fmm) {
   if (!fmm) return 0;
   FmmCtx* C = (FmmCtx*)fmm;
+  DeviceGuard guard;
   cudaSetDevice(C->dev);
   cudaDeviceSynchronize();
   delete C;
+  return 0;
+}
+int sctl_b200_fmm_set_comm(void* fmm, void* comm) {
+  if (!fmm) return set_error(SCTL_B200_ERR_ARG, "null context");
+  FmmCtx* C = (FmmCtx*)fmm;
+  std::lock_guard<std::mutex> lk(C->mu);
+  if (comm && comm_device((Comm*)comm) != C->dev)
+    return set_error(SCTL_B200_ERR_ARG, "communicator lives on device %d, the registry on device %d", comm_device((Comm*)comm), C->dev);
+  C->comm = (Comm*)comm;
   return 0;
 }
 int sctl_b200_fmm_set_accuracy(void* fmm, int digits) {
@@ -773,6 +826,7 @@ int sctl_b200_fmm_delete_src(void* fmm, const char* name) {
   if (!fmm || !name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
   FmmCtx* C = (FmmCtx*)fmm;
   std::lock_guard<std::mutex> lk(C->mu);
+  DeviceGuard guard;
   cudaSetDevice(C->dev);
   cudaDeviceSynchronize();
   bool found = false;
@@ -795,6 +849,7 @@ int sctl_b200_fmm_delete_trg(void* fmm, const char* name) {
   if (!fmm || !name) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
   FmmCtx* C = (FmmCtx*)fmm;
   std::lock_guard<std::mutex> lk(C->mu);
+  DeviceGuard guard;
   cudaSetDevice(C->dev);
   cudaDeviceSynchronize();
   bool found = false;
@@ -822,8 +877,17 @@ int sctl_b200_fmm_set_src_coord(void* fmm, const char* name, int64_t Ns, const v
   const size_t esz = elem_size(C->dtype);
   const bool dp = flags & SCTL_B200_DEVICE_PTRS;
   int rc;
-  if ((rc = fmm_upload(s->X, r_src, (size_t)Ns * 3 * esz, dp, c->stream))) return rc;
-  if (s->normal_dim && (rc = fmm_upload(s->Xn, n_src, (size_t)Ns * s->normal_dim * esz, dp, c->stream))) return rc;
+  if (fmm_multi(C)) {  // collective: every rank hands in its block; the registry holds the replica of all of them
+    if ((rc = comm_counts(C->comm, Ns, s->counts, c->stream))) return rc;
+    if ((rc = fmm_gather(C, s->X, r_src, 3 * esz, s->counts, dp, c->stream))) return rc;
+    if (s->normal_dim && (rc = fmm_gather(C, s->Xn, n_src, (size_t)s->normal_dim * esz, s->counts, dp, c->stream))) return rc;
+    Ns = 0;
+    for (int64_t v : s->counts) Ns += v;
+  } else {
+    s->counts.clear();
+    if ((rc = fmm_upload(s->X, r_src, (size_t)Ns * 3 * esz, dp, c->stream))) return rc;
+    if (s->normal_dim && (rc = fmm_upload(s->Xn, n_src, (size_t)Ns * s->normal_dim * esz, dp, c->stream))) return rc;
+  }
   CU_TRY(cudaStreamSynchronize(c->stream));  // the caller may free its buffers after the call (the reference copies, fmm-wrapper.txx:447-448)
   s->Ns = Ns;
   s->version++;
@@ -834,8 +898,16 @@ int sctl_b200_fmm_set_src_density(void* fmm, const char* name, int64_t n, const 
   FmmSrc* s = name ? C->find_src(name) : nullptr;
   if (!s) return set_error(SCTL_B200_ERR_ARG, "Source name does not exist.");
   if (n < 0 || (n > 0 && !v_src)) return set_error(SCTL_B200_ERR_ARG, "bad source density");
-  int rc = fmm_upload(s->F, v_src, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream);
-  if (rc) return rc;
+  int rc;
+  if (fmm_multi(C)) {
+    if (s->counts.empty()) return set_error(SCTL_B200_ERR_ARG, "SetSrcCoord must come first: it fixes how many sources every rank holds");
+    const int64_t mine = s->counts[(size_t)comm_rank(C->comm)];
+    if (n != mine * s->src_dim) return set_error(SCTL_B200_ERR_ARG, "density has %lld values, expected Ns_local*SrcDim = %lld", (long long)n, (long long)(mine * s->src_dim));
+    if ((rc = fmm_gather(C, s->F, v_src, (size_t)s->src_dim * elem_size(C->dtype), s->counts, flags & SCTL_B200_DEVICE_PTRS, c->stream))) return rc;
+    n = s->Ns * s->src_dim;
+  } else if ((rc = fmm_upload(s->F, v_src, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream))) {
+    return rc;
+  }
   CU_TRY(cudaStreamSynchronize(c->stream));
   s->n_den = n;
   s->version++;
@@ -846,8 +918,34 @@ int sctl_b200_fmm_set_trg_coord(void* fmm, const char* name, int64_t Nt, const v
   FmmTrg* t = name ? C->find_trg(name) : nullptr;
   if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
   if (Nt < 0 || (Nt > 0 && !r_trg)) return set_error(SCTL_B200_ERR_ARG, "bad target coordinates");
-  int rc = fmm_upload(t->X, r_trg, (size_t)Nt * 3 * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream);
-  if (rc) return rc;
+  int rc;
+  t->Nt_own = Nt;
+  t->moved = false;
+  if (fmm_multi(C)) {
+    const int rank = comm_rank(C->comm), size = comm_size(C->comm);
+    if ((rc = comm_counts(C->comm, Nt, t->counts, c->stream))) return rc;
+    int64_t total = 0, mx = 0, before = 0;
+    for (int r = 0; r < size; r++) {
+      total += t->counts[(size_t)r];
+      mx = t->counts[(size_t)r] > mx ? t->counts[(size_t)r] : mx;
+      if (r < rank) before += t->counts[(size_t)r];
+    }
+    // keep targets with their owner unless the ranks are uneven (> 5 % above the mean): then every rank evaluates block
+    // [total*r/np, total*(r+1)/np) of the concatenated set, the reference's PartitionN (fmm-wrapper.txx:504-510)
+    t->moved = total > 0 && (double)mx > 1.05 * (double)total / size + 1.0;
+    if (t->moved) {
+      t->lo = (int64_t)((__int128)total * rank / size);
+      t->hi = (int64_t)((__int128)total * (rank + 1) / size);
+      if ((rc = fmm_gather(C, t->X, r_trg, 3 * elem_size(C->dtype), t->counts, flags & SCTL_B200_DEVICE_PTRS, c->stream, true, t->lo, t->hi))) return rc;
+      Nt = t->hi - t->lo;
+    } else {
+      t->lo = before;
+      t->hi = before + Nt;
+    }
+  } else {
+    t->counts.clear();
+  }
+  if (!t->moved && (rc = fmm_upload(t->X, r_trg, (size_t)Nt * 3 * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream))) return rc;
   CU_TRY(cudaStreamSynchronize(c->stream));
   t->Nt = Nt;
   return 0;
@@ -860,8 +958,15 @@ int sctl_b200_fmm_set_src_weights(void* fmm, const char* name, int64_t n, const 
   FmmSrc* s = name ? C->find_src(name) : nullptr;
   if (!s) return set_error(SCTL_B200_ERR_ARG, "Source name does not exist.");
   if (n < 0 || (n > 0 && !wts)) return set_error(SCTL_B200_ERR_ARG, "bad source weights");
-  int rc = fmm_upload(s->W, wts, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream);
-  if (rc) return rc;
+  int rc;
+  if (fmm_multi(C) && n > 0) {
+    if (s->counts.empty()) return set_error(SCTL_B200_ERR_ARG, "SetSrcCoord must come first: it fixes how many sources every rank holds");
+    if (n != s->counts[(size_t)comm_rank(C->comm)]) return set_error(SCTL_B200_ERR_ARG, "%lld weights, expected Ns_local = %lld", (long long)n, (long long)s->counts[(size_t)comm_rank(C->comm)]);
+    if ((rc = fmm_gather(C, s->W, wts, elem_size(C->dtype), s->counts, flags & SCTL_B200_DEVICE_PTRS, c->stream))) return rc;
+    n = s->Ns;
+  } else if ((rc = fmm_upload(s->W, wts, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream))) {
+    return rc;
+  }
   CU_TRY(cudaStreamSynchronize(c->stream));
   s->n_wts = n;
   s->version++;
@@ -875,8 +980,14 @@ int sctl_b200_fmm_set_trg_normal(void* fmm, const char* name, int64_t n, const v
   if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
   if (n < 0 || (n > 0 && !n_trg)) return set_error(SCTL_B200_ERR_ARG, "bad target normals");
   if (n > 0 && t->trg_dim % 3) return set_error(SCTL_B200_ERR_ARG, "target-normal contraction needs TrgDim %% 3 == 0 (target '%s' has %d)", name, t->trg_dim);
-  int rc = fmm_upload(t->Xn, n_trg, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream);
-  if (rc) return rc;
+  int rc;
+  if (fmm_multi(C) && t->moved && n > 0) {
+    if (n != t->Nt_own * 3) return set_error(SCTL_B200_ERR_ARG, "%lld normal values, expected Nt_local*3 = %lld", (long long)n, (long long)(t->Nt_own * 3));
+    if ((rc = fmm_gather(C, t->Xn, n_trg, 3 * elem_size(C->dtype), t->counts, flags & SCTL_B200_DEVICE_PTRS, c->stream, true, t->lo, t->hi))) return rc;
+    n = t->Nt * 3;
+  } else if ((rc = fmm_upload(t->Xn, n_trg, (size_t)n * elem_size(C->dtype), flags & SCTL_B200_DEVICE_PTRS, c->stream))) {
+    return rc;
+  }
   CU_TRY(cudaStreamSynchronize(c->stream));
   t->n_nrm = n;
   return 0;
@@ -887,7 +998,7 @@ int sctl_b200_fmm_trg_count(void* fmm, const char* name, int64_t* Nt, int* trg_d
   std::lock_guard<std::mutex> lk(C->mu);
   FmmTrg* t = C->find_trg(name);
   if (!t) return set_error(SCTL_B200_ERR_ARG, "Target name does not exist.");
-  if (Nt) *Nt = t->Nt;
+  if (Nt) *Nt = t->Nt_own;
   if (trg_dim) *trg_dim = t->n_nrm ? t->trg_dim / 3 : t->trg_dim;  // values per target that eval_direct returns
   return 0;
 }
@@ -900,15 +1011,19 @@ int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t 
   const bool dotn = t->n_nrm != 0;
   if (dotn && t->n_nrm != t->Nt * 3) return set_error(SCTL_B200_ERR_ARG, "target '%s': %lld normal values, expected Nt*3 = %lld", trg_name, (long long)t->n_nrm, (long long)(t->Nt * 3));
   const int k1out = dotn ? t->trg_dim / 3 : t->trg_dim;
-  if (n != t->Nt * k1out) return set_error(SCTL_B200_ERR_ARG, "U must hold Nt*%d = %lld values", k1out, (long long)(t->Nt * k1out));
-  if (n == 0) return 0;
-  if (!U) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
+  if (n != t->Nt_own * k1out) return set_error(SCTL_B200_ERR_ARG, "U must hold Nt*%d = %lld values", k1out, (long long)(t->Nt_own * k1out));
+  const bool moved = fmm_multi(C) && t->moved;  // this rank evaluates a block of the re-partitioned targets; the potentials travel back below
+  if (n == 0 && !moved) return 0;
+  if (n > 0 && !U) return set_error(SCTL_B200_ERR_ARG, "null pointer argument");
   const size_t esz = elem_size(C->dtype);
   const bool dp = flags & SCTL_B200_DEVICE_PTRS;
   cudaStream_t st = c->stream;
-  void* dU = U;  // where the caller-visible result is produced on the device
+  void* dU = U;  // where the result of the EVALUATED targets is produced on the device
   int rc;
-  if (!dp) {
+  if (moved) {
+    if ((rc = t->Ublk.reserve((size_t)t->Nt * k1out * esz + 16))) return rc;
+    dU = t->Ublk.p;
+  } else if (!dp) {
     if ((rc = t->U.reserve((size_t)n * esz))) return rc;
     dU = t->U.p;
   }
@@ -929,7 +1044,7 @@ int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t 
                        (long long)s->n_den, (long long)(s->Ns * s->src_dim));
     if (s->n_wts && s->n_wts != s->Ns)
       return set_error(SCTL_B200_ERR_ARG, "source '%s': %lld weights, expected Ns = %lld", a.first.first.c_str(), (long long)s->n_wts, (long long)s->Ns);
-    if (s->Ns == 0) continue;
+    if (s->Ns == 0 || t->Nt == 0) continue;
     const EvalEntry& E = (C->dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[d->kernel_id];
     if (use_small_path(t->Nt, s->Ns)) {  // one launch straight from the resident AoS arrays; weights fused, no records needed
       CU_TRY(E.small[newton_level(C->dtype, C->digits)](t->X.p, s->X.p, s->normal_dim ? s->Xn.p : nullptr, s->F.p, s->n_wts ? s->W.p : nullptr, dSum, t->Nt,
@@ -946,9 +1061,23 @@ int sctl_b200_fmm_eval_direct(void* fmm, const char* trg_name, void* U, int64_t 
     if ((rc = eval_packed_device(d->kernel_id, C->dtype, t->Nt, s->Ns, t->X.p, d->rec.p, dSum, C->digits, !first, st, c->sms, nullptr))) return rc;
     first = false;
   }
-  if (first) CU_TRY(cudaMemsetAsync(dSum, 0, (size_t)n_full * esz, st));
+  if (first && n_full) CU_TRY(cudaMemsetAsync(dSum, 0, (size_t)n_full * esz, st));
   if (dotn) CU_TRY((C->dtype == SCTL_B200_F64 ? contract_normal_f64 : contract_normal_f32)(dSum, t->Xn.p, dU, t->Nt, k1out, st));
-  if (!dp) CU_TRY(cudaMemcpyAsync(U, dU, (size_t)n * esz, cudaMemcpyDeviceToHost, st));
+  if (moved) {
+    // potentials back to the ranks that own the targets (fmm-wrapper.txx:560-561): all-gather the evenly sized blocks, keep own rows
+    const int size = comm_size(C->comm);
+    int64_t total = 0;
+    for (int64_t v : t->counts) total += v;
+    std::vector<int64_t> blk((size_t)size);
+    for (int r = 0; r < size; r++) blk[(size_t)r] = (int64_t)((__int128)total * (r + 1) / size) - (int64_t)((__int128)total * r / size);
+    if ((rc = t->Ugath.reserve((size_t)total * k1out * esz + 16))) return rc;
+    if ((rc = comm_allgatherv(C->comm, dU, (size_t)k1out * esz, blk, t->Ugath.p, st))) return rc;
+    int64_t own0 = 0;
+    for (int r = 0; r < comm_rank(C->comm); r++) own0 += t->counts[(size_t)r];
+    if (n) CU_TRY(cudaMemcpyAsync(U, (const char*)t->Ugath.p + (size_t)own0 * k1out * esz, (size_t)n * esz, dp ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
+  } else if (!dp) {
+    CU_TRY(cudaMemcpyAsync(U, dU, (size_t)n * esz, cudaMemcpyDeviceToHost, st));
+  }
   CU_TRY(cudaStreamSynchronize(st));
   return 0;
 }
@@ -1138,6 +1267,7 @@ int sctl_b200_init(int ndev, const int* dev_ids) {
   return 0;
 }
 int sctl_b200_finalize(void) {
+  comm_all_gpus_release();
   std::vector<int> devs;
   {
     std::lock_guard<std::mutex> lk(g_devices_mutex);

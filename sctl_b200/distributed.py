@@ -1,4 +1,10 @@
-"""Multi-GPU driver: target sharding + source replication over NCCL (one process per GPU, torch.distributed).
+"""Multi-GPU driver: target sharding + source replication over NCCL (one process per GPU).
+
+On CUDA tensors both classes below are thin bindings of the C-ABI driver inside libsctl_b200.so (sctl_b200_comm_* /
+sctl_b200_eval_sharded* / sctl_b200_fmm_set_comm, csrc/comm.cu): the NCCL calls, the gather buffers and the evaluation are the
+library's; torch.distributed only carries the 128-byte NCCL id to the other ranks once (class LibComm). The pure-Python
+exchange further down is the same host logic over torch.distributed; it runs when a CPU `evaluator` / `local` registry is
+injected (the world-size-2 gloo tests) and for the diagnostic "ring" mode.
 
 Mirrors the per-rank structure of the reference's ParticleFMM::EvalDirect
 (/root/reference/include/sctl/fmm-wrapper.txx:490-562):
@@ -33,6 +39,56 @@ from typing import Callable, Optional
 
 import torch
 import torch.distributed as dist
+
+
+class LibComm:
+    """A communicator of libsctl_b200.so (ncclCommInitRank inside the library) spanning the ranks of a torch.distributed group:
+    rank 0 asks the library for the NCCL id, torch.distributed broadcasts its 128 bytes, every rank creates its handle on
+    its current CUDA device."""
+
+    _cache = {}
+
+    def __init__(self, group=None, device=None):
+        import ctypes
+
+        from . import capi
+
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.size = dist.get_world_size(group) if dist.is_initialized() else 1
+        dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        ident = torch.zeros(128, dtype=torch.uint8)
+        if self.size > 1:
+            if self.rank == 0:
+                buf = (ctypes.c_ubyte * 128)()
+                capi.check(capi.lib().sctl_b200_comm_unique_id(buf, 128))
+                ident = torch.tensor(list(buf), dtype=torch.uint8)
+            wire = ident.to(dev) if dist.get_backend(group) == "nccl" else ident
+            dist.broadcast(wire, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            ident = wire.cpu()
+        raw = (ctypes.c_ubyte * 128)(*ident.tolist())
+        h = ctypes.c_void_p()
+        with torch.cuda.device(dev):
+            capi.check(capi.lib().sctl_b200_set_device(dev.index))
+            capi.check(capi.lib().sctl_b200_comm_create(ctypes.byref(h), self.size, self.rank, raw))
+        self.handle, self.device = h, dev
+
+    @classmethod
+    def get(cls, group=None, device=None) -> "LibComm":
+        dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        key = (id(group) if group is not None else None, dev.index)
+        if key not in cls._cache:
+            cls._cache[key] = cls(group, dev)
+        return cls._cache[key]
+
+    def destroy(self):
+        from . import capi
+
+        h, self.handle = self.handle, None
+        if h:
+            capi.lib().sctl_b200_comm_destroy(h)
+        for k, v in list(self._cache.items()):
+            if v is self:
+                del self._cache[k]
 
 
 def partition(n: int, rank: int, size: int) -> tuple[int, int]:
@@ -75,6 +131,7 @@ class ShardedDirectSum:
             raise ValueError("mode must be 'gather' or 'ring'")
         self.kernel = kernel
         self.group = group
+        self.native = evaluator is None and mode == "gather"  # CUDA tensors go to the C-ABI driver (sctl_b200_eval_sharded_async)
         self.evaluator = evaluator or (lambda U, Xt, Xs, Xn, F, digits, overwrite: kernel.Eval(U, Xt, Xs, Xn, F, digits=digits, overwrite=overwrite))
         self.mode = mode
         self._comm_stream = None
@@ -116,11 +173,41 @@ class ShardedDirectSum:
             U = torch.zeros(nt * K1, dtype=Xt.dtype, device=Xt.device)
         if size == 1:
             return self.evaluator(U, Xt, Xs, Xn if Nd else None, F, digits, True)
+        if self.native and Xt.is_cuda:
+            return self._call_native(U, Xt, Xs, Xn if Nd else None, F, digits, counts, size)
         if counts is None:
             counts = self.source_counts(Xs.numel() // 3, Xs.device)
         if self.mode == "gather":
             return self._call_gather(U, Xt, Xs, Xn if Nd else None, F, digits, counts, rank, size)
         return self._call_ring(U, Xt, Xs, Xn if Nd else None, F, digits, counts, rank, size)
+
+    def _call_native(self, U, Xt, Xs, Xn, F, digits, counts, size):
+        """the C path: counts exchange (when not given), one ncclAllGather per source array and pack -> eval -> reduce, all
+        enqueued by libsctl_b200.so on torch's current stream; no synchronisation when `counts` is given"""
+        import ctypes
+
+        from . import capi
+
+        K0, Nd = self.kernel.SrcDim(), self.kernel.NormalDim()
+        tdt = {torch.float32: capi.F32, torch.float64: capi.F64}.get(Xt.dtype)
+        if tdt is None:
+            raise ValueError("Real must be float32 or float64")
+        ns = Xs.numel() // 3
+        for a, n, what in ((Xt, Xt.numel(), "r_trg"), (Xs, 3 * ns, "r_src"), (F, K0 * ns, "v_src"), (U, U.numel(), "v_trg")) + (((Xn, Nd * ns, "n_src"),) if Nd else ()):
+            if a.dtype != Xt.dtype or a.device != Xt.device or not a.is_contiguous() or a.numel() != n:
+                raise ValueError(f"{what}: expected a contiguous {Xt.dtype} tensor of {n} values on {Xt.device}")
+        comm = LibComm.get(self.group, Xt.device)
+        cnt = None
+        if counts is not None:
+            if len(counts) != size or counts[comm.rank] != ns:
+                raise ValueError("counts must list the number of sources of every rank")
+            cnt = (ctypes.c_int64 * size)(*counts)
+        p = lambda a: None if a is None or a.numel() == 0 else ctypes.c_void_p(a.data_ptr())
+        with torch.cuda.device(Xt.device):
+            stream = torch.cuda.current_stream().cuda_stream
+            capi.check(capi.lib().sctl_b200_eval_sharded_async(comm.handle, self.kernel.KERNEL_ID, tdt, Xt.numel() // 3, ns, p(Xt), p(Xs), p(Xn), p(F), p(U),
+                                                               digits, capi.OVERWRITE, cnt, ctypes.c_void_p(stream)))
+        return U
 
     def _allgather(self, key, local, width, counts, rank, size):
         """contiguous replica of every rank's block of one AoS array (width values per source), in a reused buffer"""
@@ -219,12 +306,17 @@ class ShardedParticleFMM:
 
         self.dtype = np.dtype(dtype or np.float64)
         self.group = group
+        self.device = torch.device(device) if device is not None else (torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu"))
+        # native: the registry of libsctl_b200.so does the exchange itself (sctl_b200_fmm_set_comm); every Set* / EvalDirect below
+        # then just forwards this rank's particles. With an injected `local` (CPU tests) the Python exchange further down runs.
+        self.native = local is None
         if local is None:
             from .fmm import ParticleFMM
 
             local = ParticleFMM(self.dtype)
+            if self._world()[1] > 1:
+                local.SetComm(LibComm.get(group, self.device))
         self.local = local
-        self.device = torch.device(device) if device is not None else (torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu"))
         self.imbalance = float(imbalance)
         self._src_counts = {}  # source name -> particles per rank
         self._src_dims = {}  # source name -> (SrcDim, NormalDim)
@@ -298,6 +390,8 @@ class ShardedParticleFMM:
 
     # -- particle data: this rank's particles in, replicas / blocks into the per-rank registry ---------------------
     def SetSrcCoord(self, name, src_coord, src_normal=None):
+        if self.native:
+            return self.local.SetSrcCoord(name, src_coord, src_normal)
         X, Xn = self._tensor(src_coord), self._tensor(src_normal)
         if X.numel() % 3:
             raise ValueError("coordinate arrays must hold 3 values per point")
@@ -315,12 +409,14 @@ class ShardedParticleFMM:
         return counts
 
     def SetSrcDensity(self, name, src_density):
+        if self.native:
+            return self.local.SetSrcDensity(name, src_density)
         F = self._tensor(src_density)
         self.local.SetSrcDensity(name, self._to_local(self._gather(F, self._src_dims[name][0], self._src_counts_of(name))))
 
     def SetSrcWeights(self, name, wts):
-        if wts is None:
-            return self.local.SetSrcWeights(name, None)
+        if self.native or wts is None:
+            return self.local.SetSrcWeights(name, wts)
         self.local.SetSrcWeights(name, self._to_local(self._gather(self._tensor(wts), 1, self._src_counts_of(name))))
 
     def _trg_block(self, name, t, width):
@@ -332,6 +428,8 @@ class ShardedParticleFMM:
         return g[width * T["lo"]:width * T["hi"]].contiguous()
 
     def SetTrgCoord(self, name, trg_coord):
+        if self.native:
+            return self.local.SetTrgCoord(name, trg_coord)
         X = self._tensor(trg_coord)
         if X.numel() % 3:
             raise ValueError("coordinate arrays must hold 3 values per point")
@@ -344,6 +442,8 @@ class ShardedParticleFMM:
         self.local.SetTrgCoord(name, self._to_local(self._trg_block(name, X, 3)))
 
     def SetTrgNormal(self, name, trg_normal):
+        if self.native:
+            return self.local.SetTrgNormal(name, trg_normal)
         T = self._trg[name]
         if trg_normal is None:
             T["out_dim"] = T["dim"]
@@ -356,6 +456,11 @@ class ShardedParticleFMM:
     # -- evaluation ----------------------------------------------------------------------------------------------
     def EvalDirect(self, trg_name, U=None):
         """potentials of THIS rank's targets from ALL ranks' sources (overwritten; fmm-wrapper.txx:500-502, :560-561)"""
+        if self.native:
+            if U is None:
+                nt, k = self.local.TrgCount(trg_name)
+                U = torch.zeros(nt * k, dtype=torch.float64 if self.dtype.itemsize == 8 else torch.float32, device=self.device)
+            return self.local.EvalDirect(trg_name, U)
         rank, size = self._world()
         T = self._trg[trg_name]
         if T["counts"] is None:

@@ -47,6 +47,18 @@ class ParticleFMM:
             except Exception:
                 pass
 
+    def SetComm(self, comm) -> None:
+        """multi-rank registry (the communicator handed to ParticleFMM(comm), fmm-wrapper.txx:204): `comm` is a
+        sctl_b200.distributed.LibComm (or None to detach). Set* calls become collective; see sctl_b200_fmm_set_comm."""
+        self._comm = comm  # keep the handle alive
+        capi.check(capi.lib().sctl_b200_fmm_set_comm(self._h, comm.handle if comm is not None else None))
+
+    def TrgCount(self, trg_name: str):
+        """(targets this rank owns, values per target that Eval returns)"""
+        nt, kd = ctypes.c_int64(), ctypes.c_int()
+        capi.check(capi.lib().sctl_b200_fmm_trg_count(self._h, trg_name.encode(), ctypes.byref(nt), ctypes.byref(kd)))
+        return nt.value, kd.value
+
     # -- registry (fmm-wrapper.txx:240-443) ---------------------------------------------------------------------
     def SetAccuracy(self, digits: int) -> None:
         capi.check(capi.lib().sctl_b200_fmm_set_accuracy(self._h, int(digits)))
@@ -77,8 +89,8 @@ class ParticleFMM:
         capi.check(capi.lib().sctl_b200_fmm_delete_trg(self._h, name.encode()))
 
     # -- particle data (fmm-wrapper.txx:444-479) -----------------------------------------------------------------
-    def _arg(self, a):
-        """-> (pointer, element count, flags, keep-alive)"""
+    def _arg(self, a, out: bool = False):
+        """-> (pointer, element count, flags, keep-alive); out=True: the array is written by the library"""
         if a is None:
             return None, 0, 0, None
         if _is_torch(a):
@@ -87,6 +99,8 @@ class ParticleFMM:
             want = {np.dtype(np.float32): torch.float32, np.dtype(np.float64): torch.float64}[self.dtype]
             if not a.is_cuda or a.dtype != want:
                 raise ValueError("torch tensors must be CUDA tensors of the context's Real type")
+            if out and not a.is_contiguous():
+                raise ValueError("the output tensor must be contiguous (a strided view would receive the result in a temporary copy)")
             a = a.contiguous()
             torch.cuda.current_stream(a.device).synchronize()  # the library copies on its own stream
             return (ctypes.c_void_p(a.data_ptr()) if a.numel() else None), a.numel(), capi.DEVICE_PTRS, a
@@ -135,7 +149,7 @@ class ParticleFMM:
         if U is not None and _is_torch(U):
             if U.numel() != n:
                 raise ValueError(f"U must hold Nt*TrgDim = {n} values")
-            p, _, fl, _k = self._arg(U)
+            p, _, fl, _k = self._arg(U, out=True)
             capi.check(capi.lib().sctl_b200_fmm_eval_direct(self._h, trg_name.encode(), p, n, fl))
             return U
         if U is None or U.size != n or U.dtype != self.dtype or not U.flags.c_contiguous:

@@ -38,3 +38,17 @@ def test_shim_matches_reference_cpu_templates(path):
     print(p.stdout[-6000:])
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
     assert "SHIM TEST PASSED" in p.stdout
+
+
+@pytest.mark.gpu
+def test_nccl_sharding_driver_matches_reference_eval_direct():
+    """tests/cpp/sharded_test: sctl_b200_comm_* / sctl_b200_eval_sharded / sctl_b200::ParticleFMM + SetComm with one rank per
+    visible GPU (ranks = threads of one process, ncclCommInitRank) against the reference's single-rank
+    ParticleFMM::EvalDirect (fmm-wrapper.txx:490-562) of the global problem; also SCTL_B200_ALL_GPUS. On a 1-GPU box the
+    communicator has one rank; scripts/gpu_multi.sh runs the same binary on 2/4/8 GPUs (profiles/r02_sharded_test_*.txt)."""
+    path = os.path.join(HERE, "cpp", "sharded_test")
+    _need(path)
+    p = subprocess.run([path], capture_output=True, text=True, timeout=900)
+    print(p.stdout[-6000:])
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
+    assert "SHARDED TEST PASSED" in p.stdout

@@ -378,11 +378,11 @@ def run_b200_arm(args):
             U_v[:] = 0
             ker.Eval(U_v, Xt_v, Xs_v, None, F_v)  # synchronous C-ABI host-pointer call (what the C++ shim calls)
     else:
+        Xt_v, Xs_v, F_v, U_v = Xt_h.numpy(), Xs_h.numpy(), F_h.numpy(), U_h.numpy()
+
         def e2e_step():
-            xt, xs, f = Xt_h.to(dev, non_blocking=True), Xs_h.to(dev, non_blocking=True), F_h.to(dev, non_blocking=True)
-            u = sharded(U, xt, xs, None, f, counts=counts)
-            U_h.copy_(u, non_blocking=True)
-            torch.cuda.synchronize()
+            # synchronous C-ABI call with HOST buffers on every rank: upload of the rank's blocks, NCCL replication, eval, download
+            sharded.eval_host(U_v, Xt_v, Xs_v, None, F_v, counts=counts, device=dev)
 
     e2e_step()  # warm-up (first host-path call creates the library stream / pool)
     barrier()
@@ -424,7 +424,7 @@ def run_b200_arm(args):
             "config": workload_config(args), "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
                     "steps": args.e2e_steps, "ms_samples": e2e_samples, "statistic": "median of the per-step max over ranks", "gpu_launches_per_step": launches_e2e,
-                    "api": "sctl_b200_eval (host pointers, C ABI)" if world == 1 else "ShardedDirectSum (pinned host shards -> NCCL -> eval -> host)"},
+                    "api": "sctl_b200_eval (host pointers, C ABI)" if world == 1 else "sctl_b200_eval_sharded (host pointers, C ABI: H2D of the rank's blocks -> ncclAllGather -> eval -> D2H)"},
             "gpu_launches": launches, "roofline": roofline, "parity": parity}
     if not args.no_cpu_baseline:  # rank 0 only (the other ranks have left), at every N: the CPU path timed beside the GPU number
         run, pairs, info = cpu_sample_runner(n, args.cpu_seconds)

@@ -209,6 +209,30 @@ class ShardedDirectSum:
                                                                digits, capi.OVERWRITE, cnt, ctypes.c_void_p(stream)))
         return U
 
+    def eval_host(self, U, Xt, Xs, Xn, F, digits: int = -1, counts: Optional[list[int]] = None, device=None):
+        """HOST numpy blocks through the C ABI (sctl_b200_eval_sharded, host pointers): this rank's blocks are uploaded by the
+        library, replicated over NCCL, evaluated, and U (numpy, overwritten) is downloaded - synchronous, like sctl_b200_eval."""
+        import ctypes
+
+        import numpy as np
+
+        from . import capi
+
+        rank, size = self._world()
+        K0, Nd, K1 = self.kernel.SrcDim(), self.kernel.NormalDim(), self.kernel.TrgDim()
+        dt = np.dtype(Xt.dtype)
+        tdt = {np.dtype(np.float32): capi.F32, np.dtype(np.float64): capi.F64}[dt]
+        nt, ns = Xt.size // 3, Xs.size // 3
+        for a, n, what in ((Xt, 3 * nt, "r_trg"), (Xs, 3 * ns, "r_src"), (F, K0 * ns, "v_src"), (U, K1 * nt, "v_trg")) + (((Xn, Nd * ns, "n_src"),) if Nd else ()):
+            if a.dtype != dt or not a.flags.c_contiguous or a.size != n:
+                raise ValueError(f"{what}: expected a contiguous {dt} array of {n} values")
+        comm = LibComm.get(self.group, device)
+        cnt = (ctypes.c_int64 * size)(*counts) if counts is not None else None
+        p = lambda a: None if a is None or a.size == 0 else a.ctypes.data_as(ctypes.c_void_p)
+        capi.check(capi.lib().sctl_b200_eval_sharded(comm.handle, self.kernel.KERNEL_ID, tdt, nt, ns, p(Xt), p(Xs), p(Xn) if Nd else None, p(F), p(U), digits,
+                                                     capi.OVERWRITE, cnt))
+        return U
+
     def _allgather(self, key, local, width, counts, rank, size):
         """contiguous replica of every rank's block of one AoS array (width values per source), in a reused buffer"""
         out = allgather_blocks(local, width, counts, rank, size, self.group, self._bufs.get(key))

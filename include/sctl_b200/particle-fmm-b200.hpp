@@ -30,6 +30,11 @@ namespace sctl_b200 {
 template <class uKernel> struct UKernelOf;
 template <class uKernel> struct UKernelOf<sctl::GenericKernel<uKernel>> { using type = uKernel; };
 
+// true for GenericKernel<K> with K one of the kernel_impl micro-kernels the library implements: lets reference code choose
+// between this class and sctl::ParticleFMM at compile time (tests/cpp/boundary_integral_b200.patch)
+template <class Kernel> struct IsDeviceKernel { static constexpr bool value = false; };
+template <class uKernel> struct IsDeviceKernel<sctl::GenericKernel<uKernel>> { static constexpr bool value = sctl_b200_shim::KernelId<uKernel>::known; };
+
 template <class Real, sctl::Integer DIM = 3> class ParticleFMM {
   static_assert(DIM == 3, "sctl_b200::ParticleFMM supports DIM == 3 (the Laplace3D / Stokes3D kernels)");
 

@@ -9,13 +9,26 @@
 //   * NearInterac / SelfInterac: an UPSAMPLED tensor GL rule (m = upsample*q per direction) on the same patch with the density
 //     interpolated from the q x q nodes (tensor Lagrange) - smooth-quadrature accuracy only, i.e. crude for the singular self
 //     interaction. That is deliberate and harmless here: both arms of the test (reference CPU templates / the B200 library)
-//     share it, the test compares ARMS, and the kernel calls inside it are themselves GenericKernel::KernelMatrix calls, so they
-//     too run through the library in the GPU arm.
+//     share it and the test compares ARMS. Like a real element list (which brings its own special quadrature), it evaluates the
+//     kernel on the HOST by default (HostKernelOf<Kernel>: the same micro-kernel under a type the shim does not match), so the
+//     library calls of the GPU arm are exactly the reference's own call sites. near_on_device() = true routes these one-target
+//     KernelMatrix calls through `ker` as well: ~2e5 tiny concurrent calls from the reference's omp loop, a stress test of the
+//     shim's small-call path.
 #ifndef SCTL_B200_TESTS_SPHERE_PATCH_LIST_HPP_
 #define SCTL_B200_TESTS_SPHERE_PATCH_LIST_HPP_
 
 #include <cmath>
 #include <vector>
+
+namespace sphere_patch_detail {
+template <class K> struct HostCopy : K {};  // same arithmetic, distinct type: never matched by the shim's specialisations
+template <class Kernel> struct HostKernelOf;
+template <class uKernel> struct HostKernelOf<sctl::GenericKernel<uKernel>> { using type = sctl::GenericKernel<HostCopy<uKernel>>; };
+inline bool& near_on_device() {
+  static bool flag = false;
+  return flag;
+}
+}  // namespace sphere_patch_detail
 
 template <class Real> class SpherePatchList : public sctl::ElementListBase<Real> {
   using Long = sctl::Long;
@@ -149,7 +162,12 @@ template <class Real> class SpherePatchList : public sctl::ElementListBase<Real>
     sctl::Vector<Real> Y, Yn, Yw;
     nodes(Y, Yn, Yw, xm_, wm_, e, e + 1);
     sctl::Matrix<Real> Mk;
-    ker.template KernelMatrix<Real, false>(Mk, Xt, Y, Yn);  // (nm*K0) x (Nt*K1): through the library in the GPU arm
+    if (sphere_patch_detail::near_on_device()) {
+      ker.template KernelMatrix<Real, false>(Mk, Xt, Y, Yn);  // (nm*K0) x (Nt*K1): through the library in the GPU arm
+    } else {
+      const typename sphere_patch_detail::HostKernelOf<Kernel>::type host_ker;
+      host_ker.template KernelMatrix<Real, false>(Mk, Xt, Y, Yn);
+    }
     if (M.Dim(0) != nq * K0 || M.Dim(1) != Nt * K1_) M.ReInit(nq * K0, Nt * K1_);
     M.SetZero();
     for (int a = 0; a < q_; a++)

@@ -52,3 +52,33 @@ def test_nccl_sharding_driver_matches_reference_eval_direct():
     print(p.stdout[-6000:])
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
     assert "SHARDED TEST PASSED" in p.stdout
+
+
+BIO_BINS = [os.path.join(HERE, "cpp", "bio_test"), os.path.join(HERE, "cpp", "bio_test_patched")]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path,args", [(BIO_BINS[0], ["8", "2"]), (BIO_BINS[1], ["8", "2"]), (BIO_BINS[0], ["--near-on-device", "5", "1"])],
+                         ids=["unmodified-reference+shim", "patched-reference", "shim+tiny-call-stress"])
+def test_boundary_integral_op_runs_on_the_library(path, args):
+    """The reference's BoundaryIntegralOp::Setup / ComputePotential (boundary_integral.txx:608-614: SetupNear's KernelMatrix calls
+    inside its own omp parallel for :949-986, ComputeFarField -> fmm.Eval :1016-1077) with a test-only ElementListBase
+    (tests/cpp/sphere_patch_list.hpp): GPU arm vs the reference's CPU templates, rel-L2 <= 1e-11, for Laplace FxU, Stokes DxU
+    (on- and off-surface targets), Laplace FxdU and Stokes FxT with the target-normal contraction, Stokes FxU f32. `patched` =
+    the same test built against a copy of boundary_integral.{hpp,txx} with tests/cpp/boundary_integral_b200.patch applied
+    (batched SetupNear, device-resident registry with fused weights / normals). `tiny-call-stress` also routes the element
+    list's own one-target near-quadrature KernelMatrix calls through the library (~1e5 concurrent calls from the reference's omp loop)."""
+    _need(path)
+    p = subprocess.run([path] + args, capture_output=True, text=True, timeout=1500)
+    print(p.stdout[-6000:])
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
+    assert "BIO TEST PASSED" in p.stdout
+
+
+def test_boundary_integral_op_reference_arm_runs_without_gpu():
+    """the test-only element list drives the UNMODIFIED reference operator on the CPU (sanity: exterior single-layer potential of
+    the unit sphere to 1e-8); keeps the BIO test infrastructure honest where it is authored"""
+    _need(BIO_BINS[0])
+    p = subprocess.run([BIO_BINS[0], "--cpu-only", "4", "1", "Laplace3D_FxU"], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
+    assert "BIO TEST PASSED" in p.stdout and "sanity" in p.stdout

@@ -605,8 +605,17 @@ static int kmat_batch_impl(int kernel_id, int dtype, int64_t nbatch, const int64
         (rc = up(d_w, src_wts, (size_t)Ns_all * esz, &p_w)) || (rc = up(d_nt, n_trg, (size_t)Nt_all * 3 * esz, &p_nt)))
       return rc;
     if ((rc = d_M.alloc((size_t)M_len * esz, st))) return rc;
-    // entries of M that no block covers keep the caller's values: stage the caller's buffer in first
-    CU_TRY(cudaMemcpyAsync(d_M.p, M, (size_t)M_len * esz, cudaMemcpyHostToDevice, st));
+    // entries of M that no block covers keep the caller's values: stage the caller's buffer in first - unless the blocks tile
+    // M exactly (the layout KernelMatrixBatch of kernel-matrix-batch-b200.hpp builds: consecutive blocks, no gaps), where the
+    // upload of a multi-GB matrix that is about to be overwritten would only cost time
+    bool tiled = true;
+    long long at = 0;
+    for (int64_t b = 0; b < nbatch && tiled; b++) {
+      tiled = (M_dsp[b] == at);
+      at += (src_dsp[b + 1] - src_dsp[b]) * ki.src_dim * (trg_dsp[b + 1] - trg_dsp[b]) * k1out;
+    }
+    tiled = tiled && at == M_len;
+    if (!tiled) CU_TRY(cudaMemcpyAsync(d_M.p, M, (size_t)M_len * esz, cudaMemcpyHostToDevice, st));
     p_M = d_M.p;
   }
   KmatBatchDesc D{};

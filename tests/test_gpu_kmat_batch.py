@@ -94,3 +94,27 @@ def test_batch_device_pointers_and_launch_count(checker):
     for b, w in enumerate(want):
         if w.size:
             assert rel_l2(Mh[M_dsp[b]:M_dsp[b] + w.size], w) <= 1e-12
+
+
+def test_batch_gaps_in_M_keep_the_callers_values(checker):
+    """host pointers: "entries of M not covered by any block are left untouched" (include/sctl_b200.h) - blocks placed with
+    gaps between them in a canary-filled M; and the gap-free layout (blocks tile M exactly, upload of M skipped) gives the same blocks"""
+    kid, dt = 4, np.float64
+    rng = np.random.default_rng(9)
+    trg_dsp, src_dsp = _batch(rng, 9, 50, 20)
+    d = capi.kernel_dims(kid)
+    Xt = synth.uniform(1, 0, 3 * trg_dsp[-1], dtype=dt)
+    Xs = synth.uniform(2, 0, 3 * src_dsp[-1], dtype=dt)
+    Xn = synth.uniform(3, 0, 3 * src_dsp[-1], dtype=dt)
+    ker = KERNELS[kid]()
+    tight, tight_dsp = ker.KernelMatrixBatch(trg_dsp, src_dsp, Xt, Xs, Xn)
+    sizes = np.diff(src_dsp) * d["src_dim"] * np.diff(trg_dsp) * d["trg_dim"]
+    gap = 17
+    M_dsp = (np.concatenate([[0], np.cumsum(sizes + gap)[:-1]]) + 5).astype(np.int64)
+    M = np.full(int((M_dsp + sizes).max()) + 11, -7.25, dtype=dt)
+    out, _ = ker.KernelMatrixBatch(trg_dsp, src_dsp, Xt, Xs, Xn, out=M, M_dsp=M_dsp)
+    covered = np.zeros(M.size, bool)
+    for b in range(sizes.size):
+        covered[M_dsp[b]:M_dsp[b] + sizes[b]] = True
+        assert np.array_equal(out[M_dsp[b]:M_dsp[b] + sizes[b]], tight[tight_dsp[b]:tight_dsp[b] + sizes[b]]), b
+    assert np.all(out[~covered] == -7.25) and (~covered).sum() >= 5 + 11

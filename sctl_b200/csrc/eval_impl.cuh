@@ -101,6 +101,75 @@ __global__ void __launch_bounds__(256) pack_kernel(const Real* __restrict__ r_sr
 }
 
 // ---------------------------------------------------------------------------------------------
+// Tile repair. The hot loops run unmasked; a pair with r2 == 0 (or subnormal r2) made rinv inf/NaN and poisoned this thread's
+// partial sums of the tile. Detect it with one add chain per target and redo the tile with the masked rsqrt (exactly-zero
+// contribution, kernel_functions.hpp:28): first the branch-free select form (zero and subnormal -> 0), and only if a POSITIVE
+// subnormal r2 was met - where the mask r2 > 0 demands a finite contribution - once more with the general rescaling form.
+// Every tile on the diagonal of a self-interaction (targets == sources) takes this path, so its speed matters at mid sizes.
+// ---------------------------------------------------------------------------------------------
+template <class Ker, class Real, int R, int NEWTON, class V>
+__device__ __forceinline__ void repair_tile(Real (&tacc)[R][Ker::NACC], const Real (&xt)[R], const Real (&yt)[R], const Real (&zt)[R], const V* tile, int ns) {
+  constexpr int REC = rec_len<Ker, Real>();
+  constexpr int NACC = Ker::NACC;
+  constexpr int NV = REC / VecOf<Real>::N;
+  bool bad = false;
+#pragma unroll
+  for (int r = 0; r < R; r++) {
+    Real sum = tacc[r][0];
+#pragma unroll
+    for (int q = 1; q < NACC; q++) sum += tacc[r][q];
+    bad |= !(fabs(sum) <= (Real)(sizeof(Real) == 8 ? 1.7976931348623157e308 : 3.402823466e38));
+  }
+  if (!bad) return;
+  bool subnormal = false;
+#pragma unroll
+  for (int r = 0; r < R; r++) {
+#pragma unroll
+    for (int q = 0; q < NACC; q++) tacc[r][q] = (Real)0;
+  }
+#pragma unroll 1
+  for (int s = 0; s < ns; s++) {
+    Real src[REC];
+#pragma unroll
+    for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const Real dx = xt[r] - src[0];
+      const Real dy = yt[r] - src[1];
+      const Real dz = zt[r] - src[2];
+      Real r2 = dx * dx;
+      r2 = fma(dy, dy, r2);
+      r2 = fma(dz, dz, r2);
+      const Real rinv = rsqrt_masked_flag<NEWTON>(r2, subnormal);
+      Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
+    }
+  }
+  if (!subnormal) return;
+#pragma unroll
+  for (int r = 0; r < R; r++) {
+#pragma unroll
+    for (int q = 0; q < NACC; q++) tacc[r][q] = (Real)0;
+  }
+#pragma unroll 1
+  for (int s = 0; s < ns; s++) {
+    Real src[REC];
+#pragma unroll
+    for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const Real dx = xt[r] - src[0];
+      const Real dy = yt[r] - src[1];
+      const Real dz = zt[r] - src[2];
+      Real r2 = dx * dx;
+      r2 = fma(dy, dy, r2);
+      r2 = fma(dz, dz, r2);
+      const Real rinv = rsqrt_masked<NEWTON>(r2);
+      Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // eval: the O(Ns*Nt) kernel
 // ---------------------------------------------------------------------------------------------
 template <class Ker, class Real, int R, int NEWTON, int MINB>
@@ -158,8 +227,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
     for (int k = 0; k < NACC; k++) acc[r][k] = 0.0;
   }
 
-  // Every tile runs UNMASKED (no r2 == 0 test in the hot loop); the rare tile that held a coincident pair is repaired below.
-  constexpr bool FAST = true;
+  // Every tile runs UNMASKED (no r2 == 0 test in the hot loop); the tile that held a coincident pair is repaired (repair_tile).
 
   for (int k = 0; k < ntile; k++) {
     const int stage = k % EVAL_STAGES;
@@ -191,43 +259,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
       }
     }
 
-    if (FAST) {
-      // A pair with r2 == 0 (or denormal) made rinv inf/NaN and poisoned this tile's partial sums: detect it
-      // with one add chain per target and redo the tile for that thread with the masked rsqrt. Tiles holding
-      // coincident points are rare (one per target when targets == sources), so the slow loop is not unrolled.
-      bool bad = false;
-#pragma unroll
-      for (int r = 0; r < R; r++) {
-        Real sum = tacc[r][0];
-#pragma unroll
-        for (int q = 1; q < NACC; q++) sum += tacc[r][q];
-        bad |= !(fabs(sum) <= (Real)(sizeof(Real) == 8 ? 1.7976931348623157e308 : 3.402823466e38));
-      }
-      if (bad) {
-#pragma unroll
-        for (int r = 0; r < R; r++) {
-#pragma unroll
-          for (int q = 0; q < NACC; q++) tacc[r][q] = (Real)0;
-        }
-#pragma unroll 1
-        for (int s = 0; s < EVAL_TILE; s++) {
-          Real src[REC];
-#pragma unroll
-          for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];
-#pragma unroll
-          for (int r = 0; r < R; r++) {
-            const Real dx = xt[r] - src[0];
-            const Real dy = yt[r] - src[1];
-            const Real dz = zt[r] - src[2];
-            Real r2 = dx * dx;
-            r2 = fma(dy, dy, r2);
-            r2 = fma(dz, dz, r2);
-            const Real rinv = rsqrt_masked<NEWTON>(r2);
-            Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
-          }
-        }
-      }
-    }
+    repair_tile<Ker, Real, R, NEWTON>(tacc, xt, yt, zt, tile, EVAL_TILE);
 
 #pragma unroll
     for (int r = 0; r < R; r++) {
@@ -281,16 +313,32 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
 // reduce: v_trg[t*K1+k] (+)= scale * sum_c partial[c][k][t]   (fixed chunk order -> deterministic)
 // ---------------------------------------------------------------------------------------------
 template <class Real, int K1>
-__global__ void __launch_bounds__(256) reduce_kernel(const double* __restrict__ partial, Real* __restrict__ v_trg, long long Nt,
+__global__ void __launch_bounds__(128) reduce_kernel(const double* __restrict__ partial, Real* __restrict__ v_trg, long long Nt,
                                                      long long nt_stride, int n_chunks, double scale, int accumulate) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= Nt) return;
   double sum[K1];
 #pragma unroll
   for (int q = 0; q < K1; q++) sum[q] = 0.0;
-  for (int c = 0; c < n_chunks; c++) {
+  // the additions run in chunk order (deterministic); the loads of 8 chunks are issued together so that a thread does not
+  // pay one memory round trip per chunk (27 chunks at 20k x 20k were 16 us of a 330 us evaluation)
+  int c = 0;
+  for (; c + 8 <= n_chunks; c += 8) {
+    double v[8][K1];
 #pragma unroll
-    for (int q = 0; q < K1; q++) sum[q] += partial[((size_t)c * K1 + q) * nt_stride + t];
+    for (int u = 0; u < 8; u++) {
+#pragma unroll
+      for (int q = 0; q < K1; q++) v[u][q] = __ldcs(partial + ((size_t)(c + u) * K1 + q) * nt_stride + t);
+    }
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+#pragma unroll
+      for (int q = 0; q < K1; q++) sum[q] += v[u][q];
+    }
+  }
+  for (; c < n_chunks; c++) {
+#pragma unroll
+    for (int q = 0; q < K1; q++) sum[q] += __ldcs(partial + ((size_t)c * K1 + q) * nt_stride + t);
   }
 #pragma unroll
   for (int q = 0; q < K1; q++) {

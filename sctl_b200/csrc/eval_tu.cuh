@@ -101,8 +101,8 @@ cudaError_t small_t(const void* r_trg, const void* r_src, const void* n_src, con
 template <class Ker>
 cudaError_t reduce_t(const double* partial, void* v_trg, long long Nt, long long nt_stride, int n_chunks, double scale, int accumulate,
                      cudaStream_t st) {
-  const unsigned blocks = (unsigned)((Nt + 255) / 256);
-  reduce_kernel<Real, Ker::K1><<<blocks, 256, 0, st>>>(partial, (Real*)v_trg, Nt, nt_stride, n_chunks, scale, accumulate);
+  const unsigned blocks = (unsigned)((Nt + 127) / 128);
+  reduce_kernel<Real, Ker::K1><<<blocks, 128, 0, st>>>(partial, (Real*)v_trg, Nt, nt_stride, n_chunks, scale, accumulate);
   count_launch();
   return cudaGetLastError();
 }

@@ -8,7 +8,7 @@
 namespace sctl_b200 {
 
 constexpr int NUM_KERNELS = 8;
-constexpr int NUM_RVAR = 2;    // register-blocking variants: [0] = small-Nt (R=1), [1] = throughput (R=4)
+constexpr int NUM_RVAR = 2;    // register-blocking variants: [0] = small-Nt (R=1), [1] = throughput (R=6; 4 for Stokes FxT)
 constexpr int NUM_NEWTON = 3;  // rsqrt refinement levels (f32 uses 0..1)
 
 struct EvalEntry {

@@ -80,6 +80,18 @@ class GenericKernel:
         return Nt, Ns
 
     @staticmethod
+    def _check_torch(a, like, numel, what):
+        """every tensor handed to the C ABI as a raw pointer: same dtype and device as r_trg, contiguous, exact size"""
+        if a.dtype != like.dtype or a.device != like.device or not a.is_contiguous() or a.numel() != numel:
+            raise ValueError(f"{what}: expected a contiguous {like.dtype} tensor of {numel} values on {like.device}, got {a.dtype} "
+                             f"{tuple(a.shape)} on {a.device}{'' if a.is_contiguous() else ' (non-contiguous)'}")
+
+    @staticmethod
+    def _check_np(a, dt, numel, what):
+        if not isinstance(a, np.ndarray) or a.dtype != dt or not a.flags.c_contiguous or a.size != numel:
+            raise ValueError(f"{what}: expected a C-contiguous {dt} array of {numel} values")
+
+    @staticmethod
     def _np_ptr(a):
         return None if a is None or a.size == 0 else a.ctypes.data_as(ctypes.c_void_p)
 
@@ -111,12 +123,16 @@ class GenericKernel:
         tdt = {torch.float32: capi.F32, torch.float64: capi.F64}.get(r_trg.dtype)
         if tdt is None:
             raise ValueError("Real must be float32 or float64")
-        for a in (r_src, v_src) + ((n_src,) if self.NormalDim() else ()):
-            if a.dtype != r_trg.dtype or a.device != r_trg.device or not a.is_contiguous():
-                raise ValueError("all arrays must be contiguous, same dtype, same device")
         Nt, Ns = self._sizes(r_trg, r_src, n_src, v_src)
+        self._check_torch(r_trg, r_trg, 3 * Nt, "r_trg")
+        self._check_torch(r_src, r_trg, 3 * Ns, "r_src")
+        self._check_torch(v_src, r_trg, self.SrcDim() * Ns, "v_src")
+        if self.NormalDim():
+            self._check_torch(n_src, r_trg, self.NormalDim() * Ns, "n_src")
         if v_trg is None or v_trg.numel() != Nt * self.TrgDim():
             v_trg = torch.zeros(Nt * self.TrgDim(), dtype=r_trg.dtype, device=r_trg.device)
+        else:  # accumulated into IN PLACE: a wrong dtype / device / stride would be an out-of-bounds device write
+            self._check_torch(v_trg, r_trg, Nt * self.TrgDim(), "v_trg")
         p = lambda a: None if a is None or a.numel() == 0 else ctypes.c_void_p(a.data_ptr())
         with torch.cuda.device(r_trg.device):
             stream = torch.cuda.current_stream().cuda_stream
@@ -131,8 +147,16 @@ class GenericKernel:
         if _is_torch(r_trg):
             import torch
 
-            tdt = {torch.float32: capi.F32, torch.float64: capi.F64}[r_trg.dtype]
+            tdt = {torch.float32: capi.F32, torch.float64: capi.F64}.get(r_trg.dtype)
+            if tdt is None or not r_trg.is_cuda:
+                raise ValueError("torch tensors must be float32 / float64 CUDA tensors")
             Nt, Ns = self._sizes(r_trg, r_src, n_src, None)
+            self._check_torch(r_trg, r_trg, 3 * Nt, "r_trg")
+            self._check_torch(r_src, r_trg, 3 * Ns, "r_src")
+            if self.NormalDim():
+                self._check_torch(n_src, r_trg, self.NormalDim() * Ns, "n_src")
+            if out is not None:
+                self._check_torch(out, r_trg, Ns * K0 * Nt * K1, "out")
             M = out if out is not None else torch.empty((Ns * K0, Nt * K1), dtype=r_trg.dtype, device=r_trg.device)
             p = lambda a: None if a is None or a.numel() == 0 else ctypes.c_void_p(a.data_ptr())
             with torch.cuda.device(r_trg.device):
@@ -144,7 +168,11 @@ class GenericKernel:
         dt = np.dtype(r_trg.dtype)
         c = lambda a: None if a is None else np.ascontiguousarray(a, dtype=dt).reshape(-1)
         r_trg, r_src, n_src = c(r_trg), c(r_src), c(n_src)
+        if dt not in _NP2DT:
+            raise ValueError("Real must be float32 or float64")
         Nt, Ns = self._sizes(r_trg, r_src, n_src, None)
+        if out is not None:
+            self._check_np(out, dt, Ns * K0 * Nt * K1, "out")
         M = out if out is not None else np.zeros((Ns * K0, Nt * K1), dtype=dt)
         capi.check(capi.lib().sctl_b200_kernel_matrix(self.KERNEL_ID, _NP2DT[dt], Nt, Ns, self._np_ptr(r_trg), self._np_ptr(r_src),
                                                       self._np_ptr(n_src) if self.NormalDim() else None, self._np_ptr(M), digits, 0))
@@ -175,7 +203,17 @@ class GenericKernel:
         if _is_torch(r_trg):
             import torch
 
-            tdt = {torch.float32: capi.F32, torch.float64: capi.F64}[r_trg.dtype]
+            tdt = {torch.float32: capi.F32, torch.float64: capi.F64}.get(r_trg.dtype)
+            if tdt is None or not r_trg.is_cuda:
+                raise ValueError("torch tensors must be float32 / float64 CUDA tensors")
+            Nt_all, Ns_all = int(trg_dsp[-1]) if nb else 0, int(src_dsp[-1]) if nb else 0
+            for a, n, what in ((r_trg, 3 * Nt_all, "r_trg"), (r_src, 3 * Ns_all, "r_src"), (n_src, self.NormalDim() * Ns_all, "n_src"), (src_wts, Ns_all, "src_wts"),
+                               (n_trg, 3 * Nt_all, "n_trg")):
+                if a is not None and (what != "n_src" or self.NormalDim()):
+                    if a.dtype != r_trg.dtype or a.device != r_trg.device or not a.is_contiguous() or a.numel() < n:
+                        raise ValueError(f"{what}: expected a contiguous {r_trg.dtype} tensor of at least {n} values on {r_trg.device}")
+            if out is not None and (out.dtype != r_trg.dtype or out.device != r_trg.device or not out.is_contiguous() or out.numel() < M_len):
+                raise ValueError(f"out: expected a contiguous {r_trg.dtype} tensor of at least {M_len} values on {r_trg.device}")
             M = out if out is not None else torch.zeros(M_len, dtype=r_trg.dtype, device=r_trg.device)
             p = lambda a: None if a is None or a.numel() == 0 else ctypes.c_void_p(a.data_ptr())
             with torch.cuda.device(r_trg.device):
@@ -187,6 +225,13 @@ class GenericKernel:
         dt = np.dtype(r_trg.dtype)
         c = lambda a: None if a is None else np.ascontiguousarray(a, dtype=dt).reshape(-1)
         r_trg, r_src, n_src, src_wts, n_trg = c(r_trg), c(r_src), c(n_src), c(src_wts), c(n_trg)
+        Nt_all, Ns_all = int(trg_dsp[-1]) if nb else 0, int(src_dsp[-1]) if nb else 0
+        for a, n, what in ((r_trg, 3 * Nt_all, "r_trg"), (r_src, 3 * Ns_all, "r_src"), (n_src if self.NormalDim() else None, self.NormalDim() * Ns_all, "n_src"),
+                           (src_wts, Ns_all, "src_wts"), (n_trg, 3 * Nt_all, "n_trg")):
+            if a is not None and a.size < n:
+                raise ValueError(f"{what}: expected at least {n} values, got {a.size}")
+        if out is not None and (not isinstance(out, np.ndarray) or out.dtype != dt or not out.flags.c_contiguous or out.size < M_len):
+            raise ValueError(f"out: expected a C-contiguous {dt} array of at least {M_len} values")
         M = out if out is not None else np.zeros(M_len, dtype=dt)
         capi.check(capi.lib().sctl_b200_kernel_matrix_batch(self.KERNEL_ID, _NP2DT[dt], nb, i64p(trg_dsp), i64p(src_dsp), i64p(M_dsp), self._np_ptr(r_trg),
                                                             self._np_ptr(r_src), self._np_ptr(n_src) if self.NormalDim() else None, self._np_ptr(src_wts),

@@ -63,6 +63,23 @@ def test_argument_errors():
         KERNELS[0]().Eval(None, np.zeros(4), np.zeros(6), None, np.zeros(2))
 
 
+def test_output_arrays_are_validated_before_the_abi_sees_them():
+    """an `out=` / v_trg handed in by the caller is written through a raw pointer: wrong dtype, size or stride must be a ValueError,
+    never an out-of-bounds write (numpy side here; the torch side is tests/test_gpu_edge_cases.py::test_torch_outputs_are_validated)"""
+    k = KERNELS[3]()
+    Xt, Xs = np.zeros(6), np.ones(9)
+    for bad in (np.zeros((9, 6), np.float32), np.zeros(53), np.zeros((9, 12))[:, ::2]):
+        with pytest.raises(ValueError):
+            k.KernelMatrix(Xt, Xs, out=bad)
+    with pytest.raises(ValueError):
+        k.Eval(np.zeros(6, np.float32), Xt, Xs, None, np.zeros(9))  # right size, wrong dtype
+    with pytest.raises(ValueError):
+        k.Eval(np.zeros(12)[::2], Xt, Xs, None, np.zeros(9))  # right size, strided
+    dsp = np.array([0, 2], np.int64)
+    with pytest.raises(ValueError):
+        k.KernelMatrixBatch(dsp, np.array([0, 3], np.int64), Xt, Xs, out=np.zeros(10))  # needs 3*3*2*3 = 54 values
+
+
 def test_no_cpu_fallback_without_device():
     if capi.device_count() > 0:
         pytest.skip("a CUDA device is present")

@@ -140,6 +140,36 @@ def test_non_finite_inputs_do_not_hang_or_spread():
     assert np.array_equal(ker.Eval(None, Xt, Xs, None, F), clean)
 
 
+def test_torch_outputs_are_validated():
+    """device-pointer entries take raw data_ptr()s: a v_trg / out of the wrong dtype, device layout or size must raise, not write"""
+    import torch
+
+    k = KERNELS[3]()
+    dev = torch.device("cuda:0")
+    Xt = torch.zeros(30, dtype=torch.float64, device=dev)
+    Xs = torch.ones(60, dtype=torch.float64, device=dev)
+    F = torch.ones(60, dtype=torch.float64, device=dev)
+    with pytest.raises(ValueError):
+        k.Eval(torch.zeros(30, dtype=torch.float32, device=dev), Xt, Xs, None, F)  # would be an 8-byte write into 4-byte slots
+    with pytest.raises(ValueError):
+        k.Eval(torch.zeros(60, dtype=torch.float64, device=dev)[::2], Xt, Xs, None, F)  # strided view
+    with pytest.raises(ValueError):
+        k.Eval(None, Xt.reshape(10, 3).t(), Xs, None, F)  # non-contiguous r_trg
+    with pytest.raises(ValueError):
+        k.KernelMatrix(Xt, Xs, out=torch.zeros(60 * 30, dtype=torch.float32, device=dev))
+    with pytest.raises(ValueError):
+        k.KernelMatrix(Xt, Xs, out=torch.zeros(60 * 30 - 1, dtype=torch.float64, device=dev))
+    from sctl_b200.fmm import ParticleFMM
+
+    fmm = ParticleFMM(np.float64)
+    fmm.AddSrc("s", k, k), fmm.AddTrg("t", k, k), fmm.SetKernelS2T("s", "t", k)
+    fmm.SetSrcCoord("s", Xs), fmm.SetSrcDensity("s", F), fmm.SetTrgCoord("t", Xt)
+    with pytest.raises(ValueError):  # a strided output would receive its result in a temporary copy
+        fmm.EvalDirect("t", torch.zeros(60, dtype=torch.float64, device=dev)[::2])
+    U = fmm.EvalDirect("t", torch.zeros(30, dtype=torch.float64, device=dev))
+    assert torch.all(torch.isfinite(U)) and float(U.abs().sum()) > 0
+
+
 def test_error_contract():
     L = capi.lib()
     p = ctypes.c_void_p(16)

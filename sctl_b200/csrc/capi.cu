@@ -258,7 +258,7 @@ static int eval_packed_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, 
   p.tiles_per_chunk = P.tiles_per_chunk;
   p.n_chunks = P.n_chunks;
   p.accumulate = accumulate ? 1 : 0;
-  p.scale = kernel_scale(kernel_id);
+  p.scale = std::ldexp(kernel_scale(kernel_id), -E.x2_shift[P.newton]);  // X2 mode accumulates an exact power of two times the sum
   CU_TRY(E.eval[P.rvar][P.newton](p, P.n_ttiles, st));
   if (ev) CU_TRY(cudaEventRecord(ev[0], st));
   if (P.n_chunks > 1) CU_TRY(E.reduce((const double*)partial.p, v_trg, Nt, P.nt_stride, P.n_chunks, p.scale, p.accumulate, st));
@@ -302,20 +302,35 @@ int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_
   return eval_packed_device(kernel_id, dtype, Nt, Ns, r_trg, rec.p, v_trg, digits, accumulate, st, sms, ev ? ev + 2 : nullptr);
 }
 
+// Sources per CTA of the KernelMatrix kernels (measured, profiles/r02l_kmat_sources_per_cta.txt). Blocks with several values
+// per target (K1out >= 3) write fastest with 8 sources per CTA at every size (Stokes FxU f64: 111 % of the measured copy
+// bandwidth against 106 % at 32; the batched SetupNear shape: 6.2 against 5.5 TB/s); thin rows (one value per target, a 16-byte
+// store per lane) want the long 32-source loop unless the grid would not even fill two waves of CTAs.
+static int kmat_sources_per_cta(long long ctas_at_32, int sms, bool thin) {
+  const long long wave = 16ll * sms;  // 16 resident 128-thread CTAs per SM
+  int sb;
+  if (thin) sb = ctas_at_32 >= 2 * wave ? 32 : (ctas_at_32 >= wave / 2 ? 16 : 8);
+  else sb = ctas_at_32 * 4 >= 2 * wave ? 8 : 4;
+  const int forced = env_int("SCTL_B200_KMAT_SB", 0);
+  return (forced == 4 || forced == 8 || forced == 16 || forced == 32) ? forced : sb;
+}
+
 static int kmat_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src, void* M,
-                       int digits, cudaStream_t st) {
+                       int digits, cudaStream_t st, int sms) {
   const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
   if (Nt == 0 || Ns == 0) return 0;
   const size_t esz = elem_size(dtype);
   const int newton = newton_level(dtype, digits);
-  // grid.y is limited to 65535 blocks of KMAT_SB sources: walk the source range in slabs
-  const int64_t slab = (int64_t)65535 * KMAT_SB;
+  const long long ct = E.kmat_cta_targets[0];
+  const int sb = kmat_sources_per_cta(((Nt + ct - 1) / ct) * ((Ns + KMAT_SB - 1) / KMAT_SB), sms, E.k1 == 1);
+  // grid.y is limited to 65535 blocks of sb sources: walk the source range in slabs
+  const int64_t slab = (int64_t)65535 * sb;
   for (int64_t s0 = 0; s0 < Ns; s0 += slab) {
     const int64_t ns = Ns - s0 < slab ? Ns - s0 : slab;
     const char* rs = (const char*)r_src + (size_t)s0 * 3 * esz;
     const char* nn = n_src ? (const char*)n_src + (size_t)s0 * E.nd * esz : nullptr;
     char* Mp = (char*)M + (size_t)s0 * E.k0 * (size_t)Nt * E.k1 * esz;
-    CU_TRY(E.kmat[newton](r_trg, rs, nn, Mp, Nt, ns, kernel_scale(kernel_id), st));
+    CU_TRY(E.kmat[newton](r_trg, rs, nn, Mp, Nt, ns, kernel_scale(kernel_id), sb, st));
   }
   return 0;
 }
@@ -526,7 +541,7 @@ static int kmat_host(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const voi
   for (int64_t s0 = 0; s0 < Ns; s0 += slab) {
     const int64_t ns = Ns - s0 < slab ? Ns - s0 : slab;
     rc = kmat_device(kernel_id, dtype, Nt, ns, d_rt.p, (const char*)d_rs.p + (size_t)s0 * 3 * esz,
-                     b_ns ? (const char*)d_ns.p + (size_t)s0 * ki.normal_dim * esz : nullptr, d_M.p, digits, st);
+                     b_ns ? (const char*)d_ns.p + (size_t)s0 * ki.normal_dim * esz : nullptr, d_M.p, digits, st, c->sms);
     if (rc) return rc;
     CU_TRY(cudaMemcpyAsync((char*)M + (size_t)s0 * row_bytes, d_M.p, (size_t)ns * row_bytes, cudaMemcpyDeviceToHost, st));
   }
@@ -563,6 +578,16 @@ static int kmat_batch_impl(int kernel_id, int dtype, int64_t nbatch, const int64
   long long* h_M = h_src + nbatch + 1;
   long long* h_cta = h_M + nbatch;
   h_cta[0] = 0;
+  int sb = KMAT_SB;
+  {  // sources per CTA: fewer when the whole batch would be only a few waves of CTAs
+    long long ctas32 = 0;
+    const long long ct = E.kmat_cta_targets[dotn];
+    for (int64_t b = 0; b < nbatch; b++) {
+      const long long nt = trg_dsp[b + 1] - trg_dsp[b], ns = src_dsp[b + 1] - src_dsp[b];
+      if (nt > 0 && ns > 0) ctas32 += ((nt + ct - 1) / ct) * ((ns + KMAT_SB - 1) / KMAT_SB);
+    }
+    sb = kmat_sources_per_cta(ctas32, c->sms, k1out == 1);
+  }
   for (int64_t b = 0; b <= nbatch; b++) {
     h_trg[b] = trg_dsp[b];
     h_src[b] = src_dsp[b];
@@ -575,7 +600,7 @@ static int kmat_batch_impl(int kernel_id, int dtype, int64_t nbatch, const int64
     if (M_dsp[b] < 0 || M_dsp[b] + len > M_len) return set_error(SCTL_B200_ERR_ARG, "block %lld does not fit in M (offset %lld + %lld > %lld)", (long long)b, (long long)M_dsp[b], len, (long long)M_len);
     h_M[b] = M_dsp[b];
     const long long ct = E.kmat_cta_targets[dotn];
-    const long long ctas = (nt && ns) ? ((nt + ct - 1) / ct) * ((ns + KMAT_SB - 1) / KMAT_SB) : 0;
+    const long long ctas = (nt && ns) ? ((nt + ct - 1) / ct) * ((ns + sb - 1) / sb) : 0;
     h_cta[b + 1] = h_cta[b] + ctas;
   }
   const long long n_ctas = h_cta[nbatch];
@@ -624,6 +649,7 @@ static int kmat_batch_impl(int kernel_id, int dtype, int64_t nbatch, const int64
   D.M_dsp = D.src_dsp + nbatch + 1;
   D.cta_dsp = D.M_dsp + nbatch;
   D.nbatch = nbatch;
+  D.sb = sb;
   CU_TRY(E.kmat_batch[dotn][newton](p_rt, p_rs, p_ns, p_w, p_nt, p_M, D, n_ctas, kernel_scale(kernel_id), st));
   if (!device_ptrs) CU_TRY(cudaMemcpyAsync(M, p_M, (size_t)M_len * esz, cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaStreamSynchronize(st));
@@ -1159,7 +1185,7 @@ int sctl_b200_kernel_matrix(int kernel_id, int dtype, int64_t Nt, int64_t Ns, co
   if (flags & SCTL_B200_DEVICE_PTRS) {
     DevCtx* c = nullptr;
     if ((rc = get_ctx(&c))) return rc;
-    if ((rc = kmat_device(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, M, digits, c->stream))) return rc;
+    if ((rc = kmat_device(kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, M, digits, c->stream, c->sms))) return rc;
     CU_TRY(cudaStreamSynchronize(c->stream));
     return 0;
   }
@@ -1175,7 +1201,7 @@ int sctl_b200_kernel_matrix_async(int kernel_id, int dtype, int64_t Nt, int64_t 
   if (flags & SCTL_B200_ALL_GPUS) return set_error(SCTL_B200_ERR_ARG, "SCTL_B200_ALL_GPUS is not supported for kernel_matrix");
   DevCtx* c = nullptr;
   if ((rc = get_ctx(&c))) return rc;
-  return kmat_device(kernel_id, dtype, Nt, Ns, d_r_trg, d_r_src, d_n_src, d_M, digits, (cudaStream_t)cuda_stream);
+  return kmat_device(kernel_id, dtype, Nt, Ns, d_r_trg, d_r_src, d_n_src, d_M, digits, (cudaStream_t)cuda_stream, c->sms);
 }
 
 int sctl_b200_kernel_matrix_batch(int kernel_id, int dtype, int64_t nbatch, const int64_t* trg_dsp, const int64_t* src_dsp, const int64_t* M_dsp,

@@ -141,6 +141,24 @@ __device__ __forceinline__ double rsqrt_unmasked(double r2, double lo_any) {
   const double q = e * p;
   return fma(y0, q, y0);
 }
+// Y = 2/sqrt(r2) after ONE Newton step with the halving deferred - the reference's own form of the iteration
+// (intrin-wrapper.hpp:519-528): y0 (3 - r2 y0^2), 3 FP instructions; the factor 2 is folded into the kernel's scale factor
+// (ukernels.cuh, X2 mode). Same quadratic convergence as the NEWTON = 1 forms above (~2^-38 in f64, ~1.5 ulp in f32).
+__device__ __forceinline__ double rsqrt_unmasked_x2(double r2, double lo_any) {
+  double seed;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(seed) : "d"(r2));
+  const double y0 = __hiloint2double(__double2hiint(seed), __double2loint(lo_any));
+  const double t = r2 * y0;
+  const double e3 = fma(-t, y0, 3.0);
+  return y0 * e3;
+}
+__device__ __forceinline__ float rsqrt_unmasked_x2(float r2, float) {
+  float y0;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y0) : "f"(r2));
+  const float t = r2 * y0;
+  const float e3 = fmaf(-t, y0, 3.0f);
+  return y0 * e3;
+}
 template <int NEWTON>
 __device__ __forceinline__ float rsqrt_unmasked(float r2, float) {
   float y0;

@@ -100,6 +100,13 @@ __global__ void __launch_bounds__(256) pack_kernel(const Real* __restrict__ r_sr
   for (int i = 0; i < REC / VecOf<Real>::N; i++) dst[i] = reinterpret_cast<const V*>(out)[i];
 }
 
+// Which instantiations run in X2 mode: the one-Newton-step refinement level - digits 5..10 in f64, and the full-precision
+// level of f32 (one step from the MUFU.RSQ seed, the reference's own count at digits = 6, intrin-wrapper.hpp:3026).
+template <class Real, int NEWTON>
+__host__ __device__ constexpr bool eval_x2() {
+  return NEWTON == 1;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Tile repair. The hot loops run unmasked; a pair with r2 == 0 (or subnormal r2) made rinv inf/NaN and poisoned this thread's
 // partial sums of the tile. Detect it with one add chain per target and redo the tile with the masked rsqrt (exactly-zero
@@ -108,7 +115,7 @@ __global__ void __launch_bounds__(256) pack_kernel(const Real* __restrict__ r_sr
 // Every tile on the diagonal of a self-interaction (targets == sources) takes this path, so its speed matters at mid sizes.
 // ---------------------------------------------------------------------------------------------
 template <class Ker, class Real, int R, int NEWTON, class V>
-__device__ __forceinline__ void repair_tile(Real (&tacc)[R][Ker::NACC], const Real (&xt)[R], const Real (&yt)[R], const Real (&zt)[R], const V* tile, int ns) {
+__device__ __forceinline__ bool repair_tile(Real (&tacc)[R][Ker::NACC], const Real (&xt)[R], const Real (&yt)[R], const Real (&zt)[R], const V* tile, int ns) {
   constexpr int REC = rec_len<Ker, Real>();
   constexpr int NACC = Ker::NACC;
   constexpr int NV = REC / VecOf<Real>::N;
@@ -120,7 +127,7 @@ __device__ __forceinline__ void repair_tile(Real (&tacc)[R][Ker::NACC], const Re
     for (int q = 1; q < NACC; q++) sum += tacc[r][q];
     bad |= !(fabs(sum) <= (Real)(sizeof(Real) == 8 ? 1.7976931348623157e308 : 3.402823466e38));
   }
-  if (!bad) return;
+  if (!bad) return false;
   bool subnormal = false;
 #pragma unroll
   for (int r = 0; r < R; r++) {
@@ -144,7 +151,7 @@ __device__ __forceinline__ void repair_tile(Real (&tacc)[R][Ker::NACC], const Re
       Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
     }
   }
-  if (!subnormal) return;
+  if (!subnormal) return true;
 #pragma unroll
   for (int r = 0; r < R; r++) {
 #pragma unroll
@@ -167,6 +174,7 @@ __device__ __forceinline__ void repair_tile(Real (&tacc)[R][Ker::NACC], const Re
       Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
     }
   }
+  return true;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -180,6 +188,9 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
   constexpr uint32_t TILE_BYTES = EVAL_TILE * REC * sizeof(Real);
   using V = typename VecOf<Real>::type;
   constexpr int NV = REC / VecOf<Real>::N;
+  // one-Newton-step level: Y = 2 rinv with the halving folded into the scale factor (ukernels.cuh "X2 mode"); the caller
+  // passes p.scale already divided by 2^X2_SHIFT (eval_x2_shift)
+  constexpr bool X2 = eval_x2<Real, NEWTON>();
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Real* tiles = reinterpret_cast<Real*>(smem_raw);
@@ -246,6 +257,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
       Real src[REC];
 #pragma unroll
       for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];  // warp-uniform LDS.128 broadcast
+      Real aux[Ker::NAUX > 0 ? Ker::NAUX : 1];
+      if (X2) Ker::prep_x2(aux, src + 3);  // once per source, shared by the R targets
 #pragma unroll
       for (int r = 0; r < R; r++) {
         const Real dx = xt[r] - src[0];
@@ -254,12 +267,22 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
         Real r2p = dx * dx;
         r2p = fma(dy, dy, r2p);
         const Real r2 = fma(dz, dz, r2p);
-        const Real rinv = rsqrt_unmasked<NEWTON>(r2, r2p);
-        Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
+        if (X2) {
+          Ker::template apply<true>(tacc[r], dx, dy, dz, rsqrt_unmasked_x2(r2, r2p), src + 3, aux);
+        } else {
+          Ker::apply(tacc[r], dx, dy, dz, rsqrt_unmasked<NEWTON>(r2, r2p), src + 3);
+        }
       }
     }
 
-    repair_tile<Ker, Real, R, NEWTON>(tacc, xt, yt, zt, tile, EVAL_TILE);
+    if (repair_tile<Ker, Real, R, NEWTON>(tacc, xt, yt, zt, tile, EVAL_TILE) && X2) {
+      // the repaired sums are the plain ones: bring them to the 2^X2_SHIFT convention of this instantiation (exact)
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+#pragma unroll
+        for (int q = 0; q < NACC; q++) tacc[r][q] *= (Real)(1 << Ker::X2_SHIFT);
+      }
+    }
 
 #pragma unroll
     for (int r = 0; r < R; r++) {

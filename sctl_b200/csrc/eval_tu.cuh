@@ -13,6 +13,9 @@ using Real = SCTL_B200_REAL;
 #ifndef SCTL_B200_RBIG
 #define SCTL_B200_RBIG 6
 #endif
+#if !defined(SCTL_B200_RBIG_F32) && SCTL_B200_RBIG == 6
+#define SCTL_B200_RBIG_F32 10
+#endif
 #ifndef SCTL_B200_MINB_BIG
 #define SCTL_B200_MINB_BIG 2
 #endif
@@ -36,7 +39,14 @@ cudaError_t pack_t(const void* r_src, const void* n_src, const void* v_src, cons
 template <int R> constexpr int minb_for() { return R > 1 ? SCTL_B200_MINB_BIG : 8; }
 // targets per thread of the throughput variant: kernels with more than 4 accumulators per target (Stokes FxT: 6)
 // take 4 so that coordinates + per-tile + running accumulators stay in registers
-template <class Ker> constexpr int rbig_for() { return (Ker::NACC > 4 && RBIG > 4) ? 4 : RBIG; }
+// FP32 (R sweep of profiles/r02j_variant_sweep.txt: R = 6/7/8/10/12 -> 1.444/1.448/1.450/1.479/1.443e12 pairs/s for Stokes FxU,
+// 221 registers at R = 10, spills at 12): 10 where the accumulators and the payload leave room, else as in f64
+template <class Ker> constexpr int rbig_for() {
+#ifdef SCTL_B200_RBIG_F32
+  if (IS_F32 && Ker::NACC <= 3 && Ker::PAY <= 4) return SCTL_B200_RBIG_F32;
+#endif
+  return (Ker::NACC > 4 && RBIG > 4) ? 4 : RBIG;
+}
 
 template <class Ker, int R, int NEWTON>
 cudaError_t eval_t(const EvalParams& p, long long n_ttiles, cudaStream_t st) {
@@ -108,14 +118,14 @@ cudaError_t reduce_t(const double* partial, void* v_trg, long long Nt, long long
 }
 
 template <class Ker, int NEWTON>
-cudaError_t kmat_t(const void* r_trg, const void* r_src, const void* n_src, void* M, long long Nt, long long Ns, double scale, cudaStream_t st) {
+cudaError_t kmat_t(const void* r_trg, const void* r_src, const void* n_src, void* M, long long Nt, long long Ns, double scale, int sb, cudaStream_t st) {
   constexpr int CT = kmat_cta_targets<Ker, Real, false>();
   const long long gx = (Nt + CT - 1) / CT;
-  const long long gy = (Ns + KMAT_SB - 1) / KMAT_SB;
+  const long long gy = (Ns + sb - 1) / sb;
   if (gy > 65535) return cudaErrorInvalidValue;  // callers slab the source range
   dim3 grid((unsigned)gx, (unsigned)gy, 1);
   kmat_kernel<Ker, Real, NEWTON><<<grid, KMAT_THREADS, 0, st>>>((const Real*)r_trg, (const Real*)r_src, (const Real*)n_src, (Real*)M, Nt, Ns,
-                                                             (Real)scale);
+                                                             (Real)scale, sb);
   count_launch();
   return cudaGetLastError();
 }
@@ -161,6 +171,9 @@ EvalEntry make_entry() {
   e.nd = Ker::ND;
   e.R[0] = RSMALL;
   e.R[1] = rbig_for<Ker>();
+  e.x2_shift[0] = eval_x2<Real, 0>() ? Ker::X2_SHIFT : 0;
+  e.x2_shift[1] = eval_x2<Real, 1>() ? Ker::X2_SHIFT : 0;
+  e.x2_shift[2] = eval_x2<Real, (IS_F32 ? 1 : 2)>() ? Ker::X2_SHIFT : 0;
   e.pack = pack_t<Ker>;
   e.reduce = reduce_t<Ker>;
   // f32 has refinement levels 0 and 1 only; level 2 aliases level 1

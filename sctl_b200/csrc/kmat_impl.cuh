@@ -11,7 +11,9 @@
 //     writes each of the K0 rows as fully coalesced stores — consecutive lanes write consecutive
 //     elements, so every store instruction covers one contiguous 32*sizeof(Real)-byte run and HBM sees
 //     whole 32-byte sectors;
-//   * source coordinates / normals are warp-uniform read-only loads (L1 broadcast).
+//   * the CTA's source coordinates / normals / row weights are staged ONCE in shared memory (coalesced) and read back as
+//     warp-uniform LDS broadcasts: with per-iteration global loads the loop sat in long-scoreboard stalls (6.9 per issue,
+//     profiles/r01z_kmat.metrics.txt) waiting for the next source's coordinates.
 #pragma once
 #include "ukernels.cuh"
 
@@ -19,7 +21,8 @@ namespace sctl_b200 {
 
 constexpr int KMAT_WARPS = 4;
 constexpr int KMAT_THREADS = KMAT_WARPS * 32;
-constexpr int KMAT_SB = 32;  // sources per CTA
+constexpr int KMAT_SB = 32;  // sources per CTA for large matrices; the launcher passes 16 / 8 / 4 when the grid would otherwise hold
+                             // only a few waves of CTAs (a 256 MB matrix is a 40-90 us kernel: one ragged wave is 15 % of it)
 
 // Kernels whose rows hold ONE value per target (Laplace FxU / DxU, and every target-normal contraction of a 3-vector) would
 // write 4- or 8-byte elements per lane: there a lane owns V = 16 B / sizeof(Real) consecutive targets and stores them as one
@@ -42,13 +45,29 @@ __host__ __device__ constexpr int kmat_cta_targets() {  // targets per CTA (bloc
 template <class Ker, class Real, int NEWTON, bool DOTN>
 __device__ __forceinline__ void kmat_block(const Real* __restrict__ r_trg, const Real* __restrict__ r_src, const Real* __restrict__ n_src,
                                            const Real* __restrict__ src_wts, const Real* __restrict__ n_trg, Real* __restrict__ M, long long Nt,
-                                           long long Ns, long long tile_x, long long slab_y, Real scale, Real* slab_all) {
+                                           long long Ns, long long tile_x, long long slab_y, Real scale, Real* slab_all, Real* srcs, int sb) {
   constexpr int K0 = Ker::K0, K1 = Ker::K1, ND = Ker::ND;
   constexpr int K1OUT = DOTN ? K1 / 3 : K1;
   constexpr int SPAN = 32 * K1OUT;  // elements per row owned by one warp
+  constexpr int SW = 3 + ND + 1;    // staged values per source: x, y, z, normal, weight * scale
 
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
+
+  // stage this CTA's sources (every thread takes part: the early exits for out-of-range warps come after the barrier)
+  const long long s_begin = slab_y * sb;
+  const long long s_end = min(Ns, s_begin + sb);
+  const int ns_cta = (int)(s_end - s_begin);
+  for (int i = threadIdx.x; i < ns_cta * 3; i += KMAT_THREADS) {
+    const int j = i / 3;
+    srcs[j * SW + (i - j * 3)] = r_src[s_begin * 3 + i];
+  }
+  for (int i = threadIdx.x; i < ns_cta * ND; i += KMAT_THREADS) {
+    const int j = i / (ND ? ND : 1);
+    srcs[j * SW + 3 + (i - j * (ND ? ND : 1))] = n_src[s_begin * ND + i];
+  }
+  for (int j = threadIdx.x; j < ns_cta; j += KMAT_THREADS) srcs[j * SW + 3 + ND] = src_wts ? src_wts[s_begin + j] * scale : scale;
+  __syncthreads();
 
   if constexpr (K1OUT == 1) {
     constexpr int V = kmat_vec<Ker, Real, DOTN>();
@@ -71,14 +90,13 @@ __device__ __forceinline__ void kmat_block(const Real* __restrict__ r_trg, const
         nt[j][2] = n_trg[tc * 3 + 2];
       }
     }
-    const long long s_begin = slab_y * KMAT_SB;
-    const long long s_end = min(Ns, s_begin + KMAT_SB);
     for (long long s = s_begin; s < s_end; s++) {
-      const Real xs = __ldg(r_src + s * 3 + 0), ys = __ldg(r_src + s * 3 + 1), zs = __ldg(r_src + s * 3 + 2);
+      const Real* sp = srcs + (int)(s - s_begin) * SW;
+      const Real xs = sp[0], ys = sp[1], zs = sp[2];
       Real n[3] = {0, 0, 0};
 #pragma unroll
-      for (int i = 0; i < ND; i++) n[i] = __ldg(n_src + s * ND + i);
-      const Real w = src_wts ? __ldg(src_wts + s) * scale : scale;
+      for (int i = 0; i < ND; i++) n[i] = sp[3 + i];
+      const Real w = sp[3 + ND];
       Real v[K0][V];
 #pragma unroll
       for (int j = 0; j < V; j++) {
@@ -131,14 +149,13 @@ __device__ __forceinline__ void kmat_block(const Real* __restrict__ r_trg, const
   const long long span_valid = min((long long)SPAN, (Nt - t0) * K1OUT);  // valid elements of this warp's span
   const long long ld = Nt * K1OUT;
 
-  const long long s_begin = slab_y * KMAT_SB;
-  const long long s_end = min(Ns, s_begin + KMAT_SB);
   for (long long s = s_begin; s < s_end; s++) {
-    const Real xs = __ldg(r_src + s * 3 + 0), ys = __ldg(r_src + s * 3 + 1), zs = __ldg(r_src + s * 3 + 2);
+    const Real* sp = srcs + (int)(s - s_begin) * SW;
+    const Real xs = sp[0], ys = sp[1], zs = sp[2];
     Real n[3] = {0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < ND; i++) n[i] = __ldg(n_src + s * ND + i);
-    const Real w = src_wts ? __ldg(src_wts + s) * scale : scale;
+    for (int i = 0; i < ND; i++) n[i] = sp[3 + i];
+    const Real w = sp[3 + ND];
     const Real dx = xt - xs, dy = yt - ys, dz = zt - zs;
     Real r2 = dx * dx;
     r2 = fma(dy, dy, r2);
@@ -185,9 +202,10 @@ __device__ __forceinline__ void kmat_block(const Real* __restrict__ r_trg, const
 template <class Ker, class Real, int NEWTON>
 __global__ void __launch_bounds__(KMAT_THREADS) kmat_kernel(const Real* __restrict__ r_trg, const Real* __restrict__ r_src,
                                                             const Real* __restrict__ n_src, Real* __restrict__ M, long long Nt,
-                                                            long long Ns, Real scale) {
+                                                            long long Ns, Real scale, int sb) {
   __shared__ Real slab[KMAT_WARPS * Ker::K0 * 32 * Ker::K1];
-  kmat_block<Ker, Real, NEWTON, false>(r_trg, r_src, n_src, nullptr, nullptr, M, Nt, Ns, blockIdx.x, blockIdx.y, scale, slab);
+  __shared__ Real srcs[KMAT_SB * (3 + Ker::ND + 1)];
+  kmat_block<Ker, Real, NEWTON, false>(r_trg, r_src, n_src, nullptr, nullptr, M, Nt, Ns, blockIdx.x, blockIdx.y, scale, slab, srcs, sb);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -203,6 +221,7 @@ struct KmatBatchDesc {
   const long long* M_dsp;    // [nbatch]   element offset of block b in M
   const long long* cta_dsp;  // [nbatch+1] prefix sum of CTAs per block
   long long nbatch;
+  int sb;                    // sources per CTA the prefix sum was built with
 };
 
 template <class Ker, class Real, int NEWTON, bool DOTN>
@@ -211,6 +230,7 @@ __global__ void __launch_bounds__(KMAT_THREADS) kmat_batch_kernel(const Real* __
                                                                   const Real* __restrict__ n_trg, Real* __restrict__ M, KmatBatchDesc D,
                                                                   long long cta0, Real scale) {
   __shared__ Real slab[KMAT_WARPS * Ker::K0 * 32 * (DOTN ? Ker::K1 / 3 : Ker::K1)];
+  __shared__ Real srcs[KMAT_SB * (3 + Ker::ND + 1)];
   const long long cta = cta0 + blockIdx.x;
   long long lo = 0, hi = D.nbatch;  // block b with cta_dsp[b] <= cta < cta_dsp[b+1]
   while (hi - lo > 1) {
@@ -225,7 +245,7 @@ __global__ void __launch_bounds__(KMAT_THREADS) kmat_batch_kernel(const Real* __
   const long long c = cta - D.cta_dsp[b];
   const long long so = D.src_dsp[b], to = D.trg_dsp[b];
   kmat_block<Ker, Real, NEWTON, DOTN>(r_trg + to * 3, r_src + so * 3, Ker::ND ? n_src + so * Ker::ND : nullptr, src_wts ? src_wts + so : nullptr,
-                                      DOTN ? n_trg + to * 3 : nullptr, M + D.M_dsp[b], Nt, Ns, c % ntx, c / ntx, scale, slab);
+                                      DOTN ? n_trg + to * 3 : nullptr, M + D.M_dsp[b], Nt, Ns, c % ntx, c / ntx, scale, slab, srcs, D.sb);
 }
 
 }  // namespace sctl_b200

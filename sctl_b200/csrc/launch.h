@@ -19,6 +19,8 @@ struct EvalEntry {
                       cudaStream_t st);
   // launches grid (n_ttiles, p.n_chunks)
   cudaError_t (*eval[NUM_RVAR][NUM_NEWTON])(const EvalParams& p, long long n_ttiles, cudaStream_t st);
+  // eval[.][newton] accumulates 2^x2_shift[newton] times the sum (X2 mode, ukernels.cuh): the caller divides p.scale by it
+  int x2_shift[NUM_NEWTON];
   // resident CTAs per SM for that instantiation (queried once)
   int (*occupancy[NUM_RVAR][NUM_NEWTON])();
   cudaError_t (*reduce)(const double* partial, void* v_trg, long long Nt, long long nt_stride, int n_chunks, double scale, int accumulate,
@@ -27,7 +29,7 @@ struct EvalEntry {
   cudaError_t (*small[NUM_NEWTON])(const void* r_trg, const void* r_src, const void* n_src, const void* v_src, const void* src_wts, void* v_trg,
                                    long long Nt, long long Ns, double scale, int accumulate, int sms, cudaStream_t st);
   cudaError_t (*kmat[NUM_NEWTON])(const void* r_trg, const void* r_src, const void* n_src, void* M, long long Nt, long long Ns, double scale,
-                                  cudaStream_t st);
+                                  int sources_per_cta, cudaStream_t st);
   int kmat_cta_targets[2];  // targets per CTA of the KernelMatrix kernels, [1] = with the target-normal contraction
   // batched small-block KernelMatrix; [1] = with the target-normal contraction (null when TrgDim is not a multiple of 3)
   cudaError_t (*kmat_batch[2][NUM_NEWTON])(const void* r_trg, const void* r_src, const void* n_src, const void* src_wts, const void* n_trg, void* M,

@@ -14,6 +14,13 @@
 //
 // FP-pipe instructions per pair, including dX (3), r^2 (3) and the full-precision rsqrt refinement (5 in
 // f64, 4 in f32): Laplace FxU 12, DxU 17, FxdU 17; Stokes FxU 22, DxU 25, FxT 27, FSxU 22, FxUP 23.
+//
+// X2 mode (one-Newton-step refinement level only): apply() is fed Y = 2*rinv, the Newton step with its halving deferred
+// exactly as the reference defers it (intrin-wrapper.hpp:519-528: y*(x*y*y - 3) scaled once at the end), which costs 3 FP
+// instructions instead of 4. A kernel that is homogeneous of degree X2_SHIFT in rinv then accumulates 2^X2_SHIFT times its
+// value and the exact power of two is folded into the scale factor. The Stokeslet-type kernels mix degrees 1 and 3: their
+// additive density term is pre-multiplied by 4 once per SOURCE (prep_x2 -> aux, NAUX values shared by all targets of the
+// thread), after which they accumulate 8x their value.
 #pragma once
 #include "common.cuh"
 
@@ -21,9 +28,11 @@ namespace sctl_b200 {
 
 struct KLaplaceFxU {  // kernel_functions.hpp:15-31
   static constexpr int K0 = 1, K1 = 1, ND = 0, PAY = 1, NACC = 1, FLOPS = 6;
+  static constexpr int X2_SHIFT = 1, NAUX = 0;
   static constexpr double SCALE_NUM = 1.0, SCALE_DEN_PI = 4.0;
   template <class Real> __device__ __forceinline__ static void pack(Real* pay, const Real*, const Real* f) { pay[0] = f[0]; }
-  template <class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real, Real, Real, Real rinv, const Real* pay) {
+  template <class Real> __device__ __forceinline__ static void prep_x2(Real*, const Real*) {}
+  template <bool X2 = false, class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real, Real, Real, Real rinv, const Real* pay, const Real* = nullptr) {
     acc[0] = fma(pay[0], rinv, acc[0]);
   }
   template <class Real> __device__ __forceinline__ static void finalize(Real (&out)[K1], const Real (&acc)[NACC]) { out[0] = acc[0]; }
@@ -34,13 +43,15 @@ struct KLaplaceFxU {  // kernel_functions.hpp:15-31
 
 struct KLaplaceDxU {  // kernel_functions.hpp:33-51
   static constexpr int K0 = 1, K1 = 1, ND = 3, PAY = 3, NACC = 1, FLOPS = 14;
+  static constexpr int X2_SHIFT = 3, NAUX = 0;
+  template <class Real> __device__ __forceinline__ static void prep_x2(Real*, const Real*) {}
   static constexpr double SCALE_NUM = 1.0, SCALE_DEN_PI = 4.0;
   template <class Real> __device__ __forceinline__ static void pack(Real* pay, const Real* n, const Real* f) {
     pay[0] = f[0] * n[0];
     pay[1] = f[0] * n[1];
     pay[2] = f[0] * n[2];
   }
-  template <class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay) {
+  template <bool X2 = false, class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay, const Real* = nullptr) {
     Real d = dx * pay[0];
     d = fma(dy, pay[1], d);
     d = fma(dz, pay[2], d);
@@ -59,9 +70,11 @@ struct KLaplaceDxU {  // kernel_functions.hpp:33-51
 
 struct KLaplaceFxdU {  // kernel_functions.hpp:53-72
   static constexpr int K0 = 1, K1 = 3, ND = 0, PAY = 1, NACC = 3, FLOPS = 11;
+  static constexpr int X2_SHIFT = 3, NAUX = 0;
   static constexpr double SCALE_NUM = -1.0, SCALE_DEN_PI = 4.0;
   template <class Real> __device__ __forceinline__ static void pack(Real* pay, const Real*, const Real* f) { pay[0] = f[0]; }
-  template <class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay) {
+  template <class Real> __device__ __forceinline__ static void prep_x2(Real*, const Real*) {}
+  template <bool X2 = false, class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay, const Real* = nullptr) {
     const Real rinv2 = rinv * rinv;
     const Real s = (pay[0] * rinv) * rinv2;
     acc[0] = fma(dx, s, acc[0]);
@@ -94,22 +107,29 @@ __device__ __forceinline__ void stokeslet_block(Real (&u)[3][3], Real dx, Real d
 
 struct KStokesFxU {  // kernel_functions.hpp:74-95
   static constexpr int K0 = 3, K1 = 3, ND = 0, PAY = 3, NACC = 3, FLOPS = 23;
+  static constexpr int X2_SHIFT = 3, NAUX = 3;
+  template <class Real> __device__ __forceinline__ static void prep_x2(Real* aux, const Real* pay) {
+    aux[0] = (Real)4 * pay[0];
+    aux[1] = (Real)4 * pay[1];
+    aux[2] = (Real)4 * pay[2];
+  }
   static constexpr double SCALE_NUM = 1.0, SCALE_DEN_PI = 8.0;
   template <class Real> __device__ __forceinline__ static void pack(Real* pay, const Real*, const Real* f) {
     pay[0] = f[0];
     pay[1] = f[1];
     pay[2] = f[2];
   }
-  // u_j += rinv * (f_j + r_j * (r.f) * rinv^2)
-  template <class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay) {
+  // u_j += rinv * (f_j + r_j * (r.f) * rinv^2);   X2: Y (4 f_j + r_j (r.f) Y^2) = 8x that
+  template <bool X2 = false, class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay, const Real* aux = nullptr) {
     Real d = dx * pay[0];
     d = fma(dy, pay[1], d);
     d = fma(dz, pay[2], d);
     const Real rinv2 = rinv * rinv;
     const Real s = d * rinv2;
-    acc[0] = fma(rinv, fma(dx, s, pay[0]), acc[0]);
-    acc[1] = fma(rinv, fma(dy, s, pay[1]), acc[1]);
-    acc[2] = fma(rinv, fma(dz, s, pay[2]), acc[2]);
+    const Real* add = X2 ? aux : pay;
+    acc[0] = fma(rinv, fma(dx, s, add[0]), acc[0]);
+    acc[1] = fma(rinv, fma(dy, s, add[1]), acc[1]);
+    acc[2] = fma(rinv, fma(dz, s, add[2]), acc[2]);
   }
   template <class Real> __device__ __forceinline__ static void finalize(Real (&out)[K1], const Real (&acc)[NACC]) {
     out[0] = acc[0];
@@ -123,6 +143,8 @@ struct KStokesFxU {  // kernel_functions.hpp:74-95
 
 struct KStokesDxU {  // kernel_functions.hpp:97-120
   static constexpr int K0 = 3, K1 = 3, ND = 3, PAY = 6, NACC = 3, FLOPS = 26;
+  static constexpr int X2_SHIFT = 5, NAUX = 0;
+  template <class Real> __device__ __forceinline__ static void prep_x2(Real*, const Real*) {}
   static constexpr double SCALE_NUM = 3.0, SCALE_DEN_PI = 4.0;
   template <class Real> __device__ __forceinline__ static void pack(Real* pay, const Real* n, const Real* f) {
     pay[0] = n[0];
@@ -133,7 +155,7 @@ struct KStokesDxU {  // kernel_functions.hpp:97-120
     pay[5] = f[2];
   }
   // u_j += r_j * (r.f)(r.n) rinv^5
-  template <class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay) {
+  template <bool X2 = false, class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay, const Real* = nullptr) {
     Real dn = dx * pay[0];
     dn = fma(dy, pay[1], dn);
     dn = fma(dz, pay[2], dn);
@@ -170,6 +192,8 @@ struct KStokesDxU {  // kernel_functions.hpp:97-120
 
 struct KStokesFxT {  // kernel_functions.hpp:122-146   u[i][j*3+k] = r_i r_j r_k rinv^5
   static constexpr int K0 = 3, K1 = 9, ND = 0, PAY = 3, NACC = 6, FLOPS = 39;
+  static constexpr int X2_SHIFT = 5, NAUX = 0;
+  template <class Real> __device__ __forceinline__ static void prep_x2(Real*, const Real*) {}
   static constexpr double SCALE_NUM = -3.0, SCALE_DEN_PI = 4.0;
   template <class Real> __device__ __forceinline__ static void pack(Real* pay, const Real*, const Real* f) {
     pay[0] = f[0];
@@ -177,7 +201,7 @@ struct KStokesFxT {  // kernel_functions.hpp:122-146   u[i][j*3+k] = r_i r_j r_k
     pay[2] = f[2];
   }
   // T_jk += r_j r_k (r.f) rinv^5 : symmetric in (j,k) -> 6 accumulators (00,01,02,11,12,22)
-  template <class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay) {
+  template <bool X2 = false, class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay, const Real* = nullptr) {
     Real d = dx * pay[0];
     d = fma(dy, pay[1], d);
     d = fma(dz, pay[2], d);
@@ -220,6 +244,12 @@ struct KStokesFxT {  // kernel_functions.hpp:122-146   u[i][j*3+k] = r_i r_j r_k
 
 struct KStokesFSxU {  // kernel_functions.hpp:148-172   Stokeslet + source/sink row u[3][j] = r_j rinv^3
   static constexpr int K0 = 4, K1 = 3, ND = 0, PAY = 4, NACC = 3, FLOPS = 26;
+  static constexpr int X2_SHIFT = 3, NAUX = 3;
+  template <class Real> __device__ __forceinline__ static void prep_x2(Real* aux, const Real* pay) {
+    aux[0] = (Real)4 * pay[0];
+    aux[1] = (Real)4 * pay[1];
+    aux[2] = (Real)4 * pay[2];
+  }
   static constexpr double SCALE_NUM = 1.0, SCALE_DEN_PI = 8.0;
   template <class Real> __device__ __forceinline__ static void pack(Real* pay, const Real*, const Real* f) {
     pay[0] = f[0];
@@ -228,15 +258,16 @@ struct KStokesFSxU {  // kernel_functions.hpp:148-172   Stokeslet + source/sink 
     pay[3] = f[3];
   }
   // u_j += rinv * (f_j + r_j * (r.f + f_3) * rinv^2)
-  template <class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay) {
+  template <bool X2 = false, class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay, const Real* aux = nullptr) {
     Real d = fma(dx, pay[0], pay[3]);
     d = fma(dy, pay[1], d);
     d = fma(dz, pay[2], d);
     const Real rinv2 = rinv * rinv;
     const Real s = d * rinv2;
-    acc[0] = fma(rinv, fma(dx, s, pay[0]), acc[0]);
-    acc[1] = fma(rinv, fma(dy, s, pay[1]), acc[1]);
-    acc[2] = fma(rinv, fma(dz, s, pay[2]), acc[2]);
+    const Real* add = X2 ? aux : pay;
+    acc[0] = fma(rinv, fma(dx, s, add[0]), acc[0]);
+    acc[1] = fma(rinv, fma(dy, s, add[1]), acc[1]);
+    acc[2] = fma(rinv, fma(dz, s, add[2]), acc[2]);
   }
   template <class Real> __device__ __forceinline__ static void finalize(Real (&out)[K1], const Real (&acc)[NACC]) {
     out[0] = acc[0];
@@ -260,21 +291,28 @@ struct KStokesFSxU {  // kernel_functions.hpp:148-172   Stokeslet + source/sink 
 
 struct KStokesFxUP {  // kernel_functions.hpp:174-198   Stokeslet + pressure column u[i][3] = r_i rinv^3
   static constexpr int K0 = 3, K1 = 4, ND = 0, PAY = 3, NACC = 4, FLOPS = 26;
+  static constexpr int X2_SHIFT = 3, NAUX = 3;
+  template <class Real> __device__ __forceinline__ static void prep_x2(Real* aux, const Real* pay) {
+    aux[0] = (Real)4 * pay[0];
+    aux[1] = (Real)4 * pay[1];
+    aux[2] = (Real)4 * pay[2];
+  }
   static constexpr double SCALE_NUM = 1.0, SCALE_DEN_PI = 8.0;
   template <class Real> __device__ __forceinline__ static void pack(Real* pay, const Real*, const Real* f) {
     pay[0] = f[0];
     pay[1] = f[1];
     pay[2] = f[2];
   }
-  template <class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay) {
+  template <bool X2 = false, class Real> __device__ __forceinline__ static void apply(Real (&acc)[NACC], Real dx, Real dy, Real dz, Real rinv, const Real* pay, const Real* aux = nullptr) {
     Real d = dx * pay[0];
     d = fma(dy, pay[1], d);
     d = fma(dz, pay[2], d);
     const Real rinv2 = rinv * rinv;
     const Real s = d * rinv2;
-    acc[0] = fma(rinv, fma(dx, s, pay[0]), acc[0]);
-    acc[1] = fma(rinv, fma(dy, s, pay[1]), acc[1]);
-    acc[2] = fma(rinv, fma(dz, s, pay[2]), acc[2]);
+    const Real* add = X2 ? aux : pay;
+    acc[0] = fma(rinv, fma(dx, s, add[0]), acc[0]);
+    acc[1] = fma(rinv, fma(dy, s, add[1]), acc[1]);
+    acc[2] = fma(rinv, fma(dz, s, add[2]), acc[2]);
     acc[3] = fma(s, rinv, acc[3]);  // p += (r.f) rinv^3
   }
   template <class Real> __device__ __forceinline__ static void finalize(Real (&out)[K1], const Real (&acc)[NACC]) {

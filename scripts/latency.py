@@ -36,7 +36,7 @@ for n in (64, 256, 1000, 2000, 4000, 8000, 16000):
 
 # host-pointer entry (what the C++ header shim calls): pageable numpy buffers in, result out, synchronous
 print("host-pointer entry sctl_b200_eval (pageable buffers, synchronous):")
-for n in (64, 256, 1000, 4000, 16000):
+for n in (64, 256, 1000, 4000, 16000, 20000):
     Xt, Xs, Xn, F = synth.make_problem(d, n, n, dt)
     U = np.zeros(n * d["trg_dim"], dtype=dt)
     hp = lambda a: None if a is None else a.ctypes.data_as(ctypes.c_void_p)

@@ -69,7 +69,7 @@ static int newton_level(int dtype, int digits) {
 // ------------------------------------------------------------------------------------------------
 // per-thread, per-device context: one non-blocking stream + timing events
 // ------------------------------------------------------------------------------------------------
-constexpr size_t STAGE_BYTES = 1u << 20;
+constexpr size_t STAGE_BYTES = 1u << 20;  // initial size of the per-thread staging arena (grows by doubling, see stage_reserve)
 // The calling thread's contexts, one per device it has used. A deque: push_back never relocates existing elements, so a
 // DevCtx* handed out by get_ctx stays valid when the thread later touches another device. The holder's destructor releases
 // streams, events and staging blocks when the thread exits (long-lived threads may also call sctl_b200_finalize).
@@ -347,33 +347,49 @@ static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
   return ms;
 }
 
-// Small host-pointer calls (all arrays together below STAGE_BYTES): the five pageable copies, five stream-ordered
-// allocations and six event records of the general path cost more than the sum itself (72 us wall at 64 x 64,
-// profiles/r01r_small_path.txt), so the arrays are gathered in a pinned block and cross the bus in one copy each way.
+// Host-pointer calls whose arrays total up to STAGE_MAX_BYTES go through a per-thread, grow-only staging ARENA: one pinned host
+// block and one device block of the same size, kept for the thread's lifetime. The general path below costs five pageable
+// copies (each staged by the driver through its own bounce buffer, one after the other), five stream-ordered allocations and
+// six event records - more than the sum itself for the call sizes the reference's in-tree callers make (72 us wall at 64 x 64,
+// +40 % at 20k x 20k, profiles/r01r_small_path.txt). Here every array is copied into the pinned block by the CPU and sent with its
+// own asynchronous copy straight away, so the CPU copy of array i+1 overlaps the bus transfer of array i; no allocation, two
+// events, one synchronisation.
+constexpr size_t STAGE_MAX_BYTES = 64u << 20;
+static int stage_reserve(DevCtx* c, size_t bytes) {
+  if (bytes <= c->stage_cap) return 0;
+  size_t cap = STAGE_BYTES;
+  while (cap < bytes) cap *= 2;
+  if (c->h_stage) cudaFreeHost(c->h_stage);
+  if (c->d_stage) cudaFree(c->d_stage);
+  c->h_stage = c->d_stage = nullptr;
+  c->stage_cap = 0;
+  cudaError_t e = cudaMallocHost(&c->h_stage, cap);
+  if (e == cudaSuccess) e = cudaMalloc(&c->d_stage, cap);
+  if (e != cudaSuccess) {
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    c->h_stage = c->d_stage = nullptr;
+    cudaGetLastError();
+    return set_error(SCTL_B200_ERR_NOMEM, "staging arena of %zu bytes: %s", cap, cudaGetErrorString(e));
+  }
+  c->stage_cap = cap;
+  return 0;
+}
+
 static int eval_host_staged(DevCtx* c, int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
                             const void* v_src, void* v_trg, int digits, bool accumulate, const size_t (&bytes)[5], const size_t (&off)[6]) {
   cudaStream_t st = c->stream;
-  if (!c->h_stage) {
-    CU_TRY(cudaMallocHost(&c->h_stage, STAGE_BYTES));
-    cudaError_t e = cudaMalloc(&c->d_stage, STAGE_BYTES);
-    if (e != cudaSuccess) {
-      cudaFreeHost(c->h_stage);
-      c->h_stage = nullptr;
-      cudaGetLastError();
-      return set_error(SCTL_B200_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", STAGE_BYTES, cudaGetErrorString(e));
-    }
-  }
+  int rc = stage_reserve(c, off[5]);
+  if (rc) return rc;
   char* h = (char*)c->h_stage;
   char* d = (char*)c->d_stage;
   const void* in[5] = {r_trg, r_src, n_src, v_src, accumulate ? v_trg : nullptr};
-  for (int i = 0; i < 5; i++)
-    if (in[i] && bytes[i]) memcpy(h + off[i], in[i], bytes[i]);
-  const size_t in_bytes = accumulate ? off[5] : off[4];
   cudaEvent_t* ev = c->ev;
   // Tiny calls: ZERO-COPY. The pinned block is mapped into the device address space (UVA), so the one-launch kernel reads
   // the arrays over the bus itself and writes v_trg straight back into host memory: one launch + one synchronisation instead
   // of copy + launch + copy (each a separate device operation of 2-3 us).
   if (off[5] <= (size_t)env_int("SCTL_B200_ZEROCOPY_MAX_BYTES", 32768) && Ns > 0 && use_small_path(Nt, Ns)) {
+    for (int i = 0; i < 5; i++)
+      if (in[i] && bytes[i]) memcpy(h + off[i], in[i], bytes[i]);
     const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
     CU_TRY(E.small[newton_level(dtype, digits)](h + off[0], h + off[1], h + off[2], h + off[3], nullptr, h + off[4], Nt, Ns, kernel_scale(kernel_id),
                                                 accumulate ? 1 : 0, c->sms, st));
@@ -383,8 +399,19 @@ static int eval_host_staged(DevCtx* c, int kernel_id, int dtype, int64_t Nt, int
     return 0;
   }
   CU_TRY(cudaEventRecord(ev[4], st));
-  CU_TRY(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, st));
-  int rc = eval_device(kernel_id, dtype, Nt, Ns, d + off[0], d + off[1], d + off[2], d + off[3], d + off[4], digits, accumulate, st, c->sms, nullptr);
+  if (off[5] <= STAGE_BYTES) {  // small: one gathered copy
+    for (int i = 0; i < 5; i++)
+      if (in[i] && bytes[i]) memcpy(h + off[i], in[i], bytes[i]);
+    const size_t in_bytes = accumulate ? off[5] : off[4];
+    CU_TRY(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, st));
+  } else {  // larger: array by array, so that the CPU copy of the next array overlaps the transfer of this one
+    for (int i = 0; i < 5; i++) {
+      if (!in[i] || !bytes[i]) continue;
+      memcpy(h + off[i], in[i], bytes[i]);
+      CU_TRY(cudaMemcpyAsync(d + off[i], h + off[i], bytes[i], cudaMemcpyHostToDevice, st));
+    }
+  }
+  rc = eval_device(kernel_id, dtype, Nt, Ns, d + off[0], d + off[1], d + off[2], d + off[3], d + off[4], digits, accumulate, st, c->sms, nullptr);
   if (rc) return rc;
   CU_TRY(cudaMemcpyAsync(h + off[4], d + off[4], bytes[4], cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaEventRecord(ev[5], st));
@@ -409,7 +436,7 @@ static int eval_host_one_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns
                              (size_t)Nt * ki.trg_dim * esz};
     size_t off[6] = {0, 0, 0, 0, 0, 0};
     for (int i = 0; i < 5; i++) off[i + 1] = off[i] + (bytes[i] + 255) / 256 * 256;
-    if (off[5] <= STAGE_BYTES && (size_t)env_int("SCTL_B200_STAGE_MAX_BYTES", (int)STAGE_BYTES) >= off[5])
+    if (off[5] <= STAGE_MAX_BYTES && (size_t)env_int("SCTL_B200_STAGE_MAX_BYTES", (int)STAGE_MAX_BYTES) >= off[5])
       return eval_host_staged(c, kernel_id, dtype, Nt, Ns, r_trg, r_src, n_src, v_src, v_trg, digits, accumulate, bytes, off);
   }
   DevAlloc d_rt, d_rs, d_ns, d_vs, d_vt;

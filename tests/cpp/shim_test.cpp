@@ -12,6 +12,7 @@
 //
 // Modes:  shim_test            full comparison (needs a GPU; exit 0 iff all within tolerance)
 //         shim_test --no-gpu   checks that a compute call fails LOUDLY (abort through SCTL_ERROR) without a GPU
+//         shim_test --bad-normal  checks that a source-normal vector of the wrong length aborts (needs a GPU)
 #include <sctl.hpp>
 #include <sctl_b200/generic-kernel-b200.hpp>
 #include <sctl_b200/particle-fmm-b200.hpp>
@@ -163,6 +164,18 @@ int main(int argc, char** argv) {
     fill(Xt), fill(Xs), fill(F);
     ker.Eval<double, true>(U, Xt, Xs, Xn, F);
     std::printf("UNEXPECTED: Eval returned without a GPU (silent fallback?)\n");
+    return 0;
+  }
+  if (argc > 1 && !std::strcmp(argv[1], "--bad-normal")) {
+    // expected: SCTL_ASSERT -> abort(): the reference asserts Xn.Dim() == Ns*NorDim (fmm-wrapper.txx:535); the C ABI takes no
+    // length for the normals, so the wrapper must refuse a short vector instead of letting the library read past it
+    sctl::Stokes3D_DxU dl;
+    sctl_b200::ParticleFMM<double, 3> fmm;
+    fmm.AddSrc("DL", dl, dl);
+    sctl::Vector<double> X(30), Xn(12);
+    fill(X), fill(Xn);
+    fmm.SetSrcCoord("DL", X, Xn);
+    std::printf("UNEXPECTED: SetSrcCoord accepted 12 normal values for 10 sources\n");
     return 0;
   }
   sctl::Profile::Enable(true);

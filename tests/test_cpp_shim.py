@@ -30,6 +30,16 @@ def test_shim_fails_loudly_without_gpu(path):
 
 
 @pytest.mark.gpu
+def test_registry_wrapper_aborts_on_a_short_normal_vector():
+    """sctl_b200::ParticleFMM::SetSrcCoord with 12 normal values for 10 sources must abort like the reference's assert
+    (fmm-wrapper.txx:535) - the C ABI has no length argument for the normals"""
+    _need(BINS[0])
+    p = subprocess.run([BINS[0], "--bad-normal"], capture_output=True, text=True, timeout=120)
+    assert p.returncode != 0, p.stdout
+    assert "UNEXPECTED" not in p.stdout
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("path", BINS, ids=["plain", "memdebug"])
 def test_shim_matches_reference_cpu_templates(path):
     """all 8 kernels x f32/f64: Eval, accumulate, type-erased static Eval, KernelMatrix shapes, ParticleFMM::EvalDirect"""

@@ -226,8 +226,9 @@ SCTL_B200_API int sctl_b200_last_timing(double ms[5]);
 
 /* Test hooks (tests/test_gpu_rsqrt.py). sctl_b200_newton_level: the rsqrt refinement level (0 seed, 1 one Newton step, 2 full
  * precision) the kernels use for `digits`; -1 for a bad dtype. No GPU needed. sctl_b200_test_rsqrt: y[i] = the device rsqrt of
- * that level applied to x[i] (HOST pointers), mode 1 = the masked form of the one-launch / KernelMatrix kernels and of
- * repaired tiles (x > 0 ? 1/sqrt(x) : 0, approx_rsqrt<digits>(x, x > 0) of vec.txx:361-364), mode 0 / 2 = the unmasked form
+ * that level applied to x[i] (HOST pointers), mode 1 = the masked form of the one-launch /
+ * KernelMatrix kernels and mode 3 the branch-free form of repaired tiles (both: x > 0 ? 1/sqrt(x) : 0,
+ * approx_rsqrt<digits>(x, x > 0) of vec.txx:361-364), mode 0 / 2 = the unmasked form
  * of the tiled hot loop with an arbitrary / worst-case low word in the seed (x <= 0 or subnormal gives inf or NaN there). */
 SCTL_B200_API int sctl_b200_newton_level(int dtype, int digits);
 SCTL_B200_API int sctl_b200_test_rsqrt(int dtype, int newton, int mode, int64_t n, const void* x, void* y);

@@ -22,6 +22,8 @@ for v in "$@"; do
     u1) build u1 -DSCTL_B200_UNROLL=1 ;;
     u4) build u4 -DSCTL_B200_UNROLL=4 ;;
     tile256) build tile256 -DSCTL_B200_EVAL_TILE=256 ;;
+    repair:*) # repair:MODE  (SCTL_B200_REPAIR_MODE sweep of eval_impl.cuh)
+      build repair${v#repair:} -DSCTL_B200_REPAIR_MODE=${v#repair:} ;;
     custom:*) # custom:name:R:MINB:THREADS:UNROLL[:TILE[:STAGES]]
       IFS=: read -r _ n R M T U TL ST <<< "$v"
       build $n -DSCTL_B200_RBIG=$R -DSCTL_B200_MINB_BIG=$M -DSCTL_B200_EVAL_THREADS=$T -DSCTL_B200_UNROLL=$U -DSCTL_B200_EVAL_TILE=${TL:-128} -DSCTL_B200_EVAL_STAGES=${ST:-4} ;;

@@ -13,5 +13,6 @@ SCTL_B200_BENCH_N=1000000 timeout 600 $TR bench.py --impl reference --gpus $N --
 timeout 900 python scripts/bench_all_gpus.py ${ALLGPU_N:-1000000} 3 3 > $OUT/all_gpus_n$N.txt 2>&1; echo "all_gpus exit $?"; cat $OUT/all_gpus_n$N.txt
 if [ -n "$FULL" ]; then
   SCTL_B200_BENCH_VERBOSE=1 timeout 1500 $TR bench.py --gpus $N --steps 2 --warmup 3 > $OUT/bench_n${N}.json 2> $OUT/bench_n${N}.err; echo "bench C3 exit $?"; cat $OUT/bench_n${N}.json
-  timeout 1500 python scripts/bench_all_gpus.py 4000000 3 2 > $OUT/all_gpus_c3_n$N.txt 2>&1; cat $OUT/all_gpus_c3_n$N.txt
+  timeout 1500 python scripts/bench_all_gpus.py 4000000 3 1 > $OUT/all_gpus_c3_n$N.txt 2>&1; cat $OUT/all_gpus_c3_n$N.txt
+  timeout 1500 $TR tests/tools/bench_configs_multi.py C4 C5 > $OUT/configs_n$N.txt 2>&1; echo "configs exit $?"; grep -vE "^\[|^W|^\*" $OUT/configs_n$N.txt | tail -12
 fi

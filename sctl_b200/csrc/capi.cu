@@ -1021,7 +1021,18 @@ int sctl_b200_fmm_set_src_weights(void* fmm, const char* name, int64_t n, const 
   if (!s) return set_error(SCTL_B200_ERR_ARG, "Source name does not exist.");
   if (n < 0 || (n > 0 && !wts)) return set_error(SCTL_B200_ERR_ARG, "bad source weights");
   int rc;
-  if (fmm_multi(C) && n > 0) {
+  if (fmm_multi(C)) {
+    // collective in multi-rank mode, also for a rank that holds no sources: the ranks first agree whether weights are being
+    // set (some rank passes n > 0) or removed (every rank passes 0)
+    std::vector<int64_t> wc;
+    if ((rc = comm_counts(C->comm, n, wc, c->stream))) return rc;
+    int64_t total = 0;
+    for (int64_t v : wc) total += v;
+    if (total == 0) {
+      s->n_wts = 0;
+      s->version++;
+      return 0;
+    }
     if (s->counts.empty()) return set_error(SCTL_B200_ERR_ARG, "SetSrcCoord must come first: it fixes how many sources every rank holds");
     if (n != s->counts[(size_t)comm_rank(C->comm)]) return set_error(SCTL_B200_ERR_ARG, "%lld weights, expected Ns_local = %lld", (long long)n, (long long)s->counts[(size_t)comm_rank(C->comm)]);
     if ((rc = fmm_gather(C, s->W, wts, elem_size(C->dtype), s->counts, flags & SCTL_B200_DEVICE_PTRS, c->stream))) return rc;
@@ -1043,7 +1054,16 @@ int sctl_b200_fmm_set_trg_normal(void* fmm, const char* name, int64_t n, const v
   if (n < 0 || (n > 0 && !n_trg)) return set_error(SCTL_B200_ERR_ARG, "bad target normals");
   if (n > 0 && t->trg_dim % 3) return set_error(SCTL_B200_ERR_ARG, "target-normal contraction needs TrgDim %% 3 == 0 (target '%s' has %d)", name, t->trg_dim);
   int rc;
-  if (fmm_multi(C) && t->moved && n > 0) {
+  if (fmm_multi(C) && t->moved) {
+    // collective (the targets were re-partitioned): ranks that own no target take part too; all-zero = remove the normals
+    std::vector<int64_t> nc;
+    if ((rc = comm_counts(C->comm, n, nc, c->stream))) return rc;
+    int64_t total = 0;
+    for (int64_t v : nc) total += v;
+    if (total == 0) {
+      t->n_nrm = 0;
+      return 0;
+    }
     if (n != t->Nt_own * 3) return set_error(SCTL_B200_ERR_ARG, "%lld normal values, expected Nt_local*3 = %lld", (long long)n, (long long)(t->Nt_own * 3));
     if ((rc = fmm_gather(C, t->Xn, n_trg, 3 * elem_size(C->dtype), t->counts, flags & SCTL_B200_DEVICE_PTRS, c->stream, true, t->lo, t->hi))) return rc;
     n = t->Nt * 3;

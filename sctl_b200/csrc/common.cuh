@@ -90,6 +90,28 @@ __device__ __forceinline__ double rsqrt_masked(double r2) {
 // was seen, in which case the caller repeats the tile with rsqrt_masked above. Costs ISETP + SEL + a few predicate ops per
 // pair instead of a divergent branch: the repair of a tile that holds coincident points (every tile on the diagonal of a
 // self-interaction) then runs close to the speed of the unmasked loop instead of 4x slower.
+// Branch-free AND complete: the r2 > 0 mask with subnormal r2 handled by selects - the seed is taken of r2 * 2^108 when r2 is
+// below the normal range (exact scaling; MUFU flushes subnormals) and multiplied by 2^54 afterwards, and it is zeroed only for
+// r2 == 0. One loop, no flag, no second pass; a few more integer / FP64 instructions per pair than rsqrt_masked_flag, which
+// only the repair path of eval_kernel pays.
+template <int NEWTON>
+__device__ __forceinline__ double rsqrt_masked_sel(double r2) {
+  const int rh = __double2hiint(r2);
+  const bool ok = rh >= 0x00100000;                    // positive normal number
+  const bool nonzero = (rh | __double2loint(r2)) != 0;  // r2 is a sum of squares: never negative
+  const double xs = ok ? r2 : r2 * 0x1p108;
+  double seed;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(seed) : "d"(xs));
+  double y0 = __hiloint2double(nonzero ? __double2hiint(seed) : 0, 0);
+  y0 = ok ? y0 : y0 * 0x1p54;
+  if (NEWTON == 0) return y0;
+  const double t = r2 * y0;
+  const double e = fma(-t, y0, 1.0);
+  if (NEWTON == 1) return fma(0.5 * y0, e, y0);
+  const double p = fma(e, 0.375, 0.5);
+  const double q = e * p;
+  return fma(y0, q, y0);
+}
 template <int NEWTON>
 __device__ __forceinline__ double rsqrt_masked_flag(double r2, bool& subnormal) {
   double seed;
@@ -181,6 +203,20 @@ __device__ __forceinline__ float rsqrt_pos_normal(float r2) {
   const float e = fmaf(-t, y0, 1.0f);
   const float h = 0.5f * y0;
   return fmaf(h, e, y0);
+}
+template <int NEWTON>
+__device__ __forceinline__ float rsqrt_masked_sel(float r2) {
+  const int rb = __float_as_int(r2);
+  const bool ok = rb >= 0x00800000;
+  const float xs = ok ? r2 : r2 * 0x1p48f;
+  float seed;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"(xs));
+  float y0 = rb != 0 ? seed : 0.0f;
+  y0 = ok ? y0 : y0 * 0x1p24f;
+  if (NEWTON == 0) return y0;
+  const float t = r2 * y0;
+  const float e = fmaf(-t, y0, 1.0f);
+  return fmaf(0.5f * y0, e, y0);
 }
 template <int NEWTON>
 __device__ __forceinline__ float rsqrt_masked_flag(float r2, bool& subnormal) {

@@ -109,25 +109,29 @@ __host__ __device__ constexpr bool eval_x2() {
 
 // ---------------------------------------------------------------------------------------------
 // Tile repair. The hot loops run unmasked; a pair with r2 == 0 (or subnormal r2) made rinv inf/NaN and poisoned this thread's
-// partial sums of the tile. Detect it with one add chain per target and redo the tile with the masked rsqrt (exactly-zero
-// contribution, kernel_functions.hpp:28): first the branch-free select form (zero and subnormal -> 0), and only if a POSITIVE
-// subnormal r2 was met - where the mask r2 > 0 demands a finite contribution - once more with the general rescaling form.
-// Every tile on the diagonal of a self-interaction (targets == sources) takes this path, so its speed matters at mid sizes.
+// partial sums of the tile. Detect it with one add chain per target and redo the tile with the masked rsqrt in its branch-free
+// form (rsqrt_masked_sel): exactly-zero contribution for r2 == 0 (kernel_functions.hpp:28) and a finite rinv for every
+// positive r2, subnormal ones included. Every tile on the diagonal of a self-interaction (targets == sources) takes this path,
+// so its speed matters at mid sizes (185 SASS instructions per source against 147 in the hot loop; the branchy general form
+// was 277).
 // ---------------------------------------------------------------------------------------------
-template <class Ker, class Real, int R, int NEWTON, class V>
-__device__ __forceinline__ bool repair_tile(Real (&tacc)[R][Ker::NACC], const Real (&xt)[R], const Real (&yt)[R], const Real (&zt)[R], const V* tile, int ns) {
+#ifndef SCTL_B200_REPAIR_MODE
+#define SCTL_B200_REPAIR_MODE 7
+#endif
+// How the repair is coded matters to the HOT loop, although it never runs there: the repair code shares the kernel's register
+// allocation, and the hot loop's FP64-pipe rate depends on the exact register (bank) assignment of its DFMA operands. Measured
+// on B200, Stokes FxU f64 at N = 262144 (profiles/r02q_repair_mode_sweep.txt; round-1 library: 90.2 ms):
+//   7  ONE branch-free loop with rsqrt_masked_sel (zero -> 0, subnormal rescaled by selects)              90.1 ms  <- default
+//   3  one loop with the select form that sends subnormal r2 to 0 (round 1's semantics, not the mask's)    90.1 ms
+//   0  select loop with a "positive subnormal seen" flag + a second, general loop, both inline            91.5 ms
+//   (second loop one target at a time, inline or through a small __noinline__ function: 91.5 / 91.7 ms; second loop or both
+//    loops out of line with their arguments in a local-memory struct: 92.1 / 92.4 ms - variants removed again)
+// Same 147 SASS instructions in the hot loop in every case; only the register numbers differ.
+template <class Ker, class Real, int R, int NEWTON, int FORM, class V>
+__device__ __forceinline__ bool repair_loop(Real (&tacc)[R][Ker::NACC], const Real (&xt)[R], const Real (&yt)[R], const Real (&zt)[R], const V* tile, int ns) {
   constexpr int REC = rec_len<Ker, Real>();
   constexpr int NACC = Ker::NACC;
   constexpr int NV = REC / VecOf<Real>::N;
-  bool bad = false;
-#pragma unroll
-  for (int r = 0; r < R; r++) {
-    Real sum = tacc[r][0];
-#pragma unroll
-    for (int q = 1; q < NACC; q++) sum += tacc[r][q];
-    bad |= !(fabs(sum) <= (Real)(sizeof(Real) == 8 ? 1.7976931348623157e308 : 3.402823466e38));
-  }
-  if (!bad) return false;
   bool subnormal = false;
 #pragma unroll
   for (int r = 0; r < R; r++) {
@@ -147,32 +151,32 @@ __device__ __forceinline__ bool repair_tile(Real (&tacc)[R][Ker::NACC], const Re
       Real r2 = dx * dx;
       r2 = fma(dy, dy, r2);
       r2 = fma(dz, dz, r2);
-      const Real rinv = rsqrt_masked_flag<NEWTON>(r2, subnormal);
+      // FORM 0: branch-free and complete; 1: branch-free, subnormal -> 0 + flag; 2: general form with branches
+      const Real rinv = FORM == 0 ? rsqrt_masked_sel<NEWTON>(r2) : (FORM == 1 ? rsqrt_masked_flag<NEWTON>(r2, subnormal) : rsqrt_masked<NEWTON>(r2));
       Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
     }
   }
-  if (!subnormal) return true;
+  return subnormal;
+}
+
+template <class Ker, class Real, int R, int NEWTON, class V>
+__device__ __forceinline__ bool repair_tile(Real (&tacc)[R][Ker::NACC], const Real (&xt)[R], const Real (&yt)[R], const Real (&zt)[R], const V* tile, int ns) {
+  constexpr int NACC = Ker::NACC;
+  bool bad = false;
 #pragma unroll
   for (int r = 0; r < R; r++) {
+    Real sum = tacc[r][0];
 #pragma unroll
-    for (int q = 0; q < NACC; q++) tacc[r][q] = (Real)0;
+    for (int q = 1; q < NACC; q++) sum += tacc[r][q];
+    bad |= !(fabs(sum) <= (Real)(sizeof(Real) == 8 ? 1.7976931348623157e308 : 3.402823466e38));
   }
-#pragma unroll 1
-  for (int s = 0; s < ns; s++) {
-    Real src[REC];
-#pragma unroll
-    for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];
-#pragma unroll
-    for (int r = 0; r < R; r++) {
-      const Real dx = xt[r] - src[0];
-      const Real dy = yt[r] - src[1];
-      const Real dz = zt[r] - src[2];
-      Real r2 = dx * dx;
-      r2 = fma(dy, dy, r2);
-      r2 = fma(dz, dz, r2);
-      const Real rinv = rsqrt_masked<NEWTON>(r2);
-      Ker::apply(tacc[r], dx, dy, dz, rinv, src + 3);
-    }
+  if (!bad) return false;
+  constexpr int MODE = SCTL_B200_REPAIR_MODE;
+  if (MODE == 7) {
+    repair_loop<Ker, Real, R, NEWTON, 0>(tacc, xt, yt, zt, tile, ns);
+  } else {
+    const bool subnormal = repair_loop<Ker, Real, R, NEWTON, 1>(tacc, xt, yt, zt, tile, ns);
+    if (MODE == 0 && subnormal) repair_loop<Ker, Real, R, NEWTON, 2>(tacc, xt, yt, zt, tile, ns);
   }
   return true;
 }

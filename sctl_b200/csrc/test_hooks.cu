@@ -13,6 +13,7 @@ namespace {
 // mode 0: rsqrt_unmasked, the seed's undefined low word taken from x itself (arbitrary mantissa bits)
 // mode 1: rsqrt_masked  (r2 > 0 mask, subnormal rescaling)
 // mode 2: rsqrt_unmasked with the seed's low word all ones (worst-case perturbation of the seed)
+// mode 3: rsqrt_masked_sel (the branch-free complete form of the tile-repair loop)
 __device__ __forceinline__ double all_ones_lo(double) { return __hiloint2double(0, -1); }
 __device__ __forceinline__ float all_ones_lo(float) { return 0.0f; }  // the f32 seed has no undefined bits
 
@@ -24,6 +25,8 @@ __global__ void rsqrt_test_kernel(const Real* __restrict__ x, Real* __restrict__
   Real r;
   if (mode == 1) {
     r = rsqrt_masked<NEWTON>(v);
+  } else if (mode == 3) {
+    r = rsqrt_masked_sel<NEWTON>(v);
   } else if (mode == 2) {
     r = rsqrt_unmasked<NEWTON>(v, all_ones_lo(v));
   } else {
@@ -59,7 +62,7 @@ cudaError_t run(int newton, int mode, long long n, const void* hx, void* hy) {
 }  // namespace sctl_b200
 
 extern "C" int sctl_b200_test_rsqrt(int dtype, int newton, int mode, int64_t n, const void* x, void* y) {
-  if ((dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) || newton < 0 || newton > 2 || mode < 0 || mode > 2 || n < 0 || (n > 0 && (!x || !y)))
+  if ((dtype != SCTL_B200_F32 && dtype != SCTL_B200_F64) || newton < 0 || newton > 2 || mode < 0 || mode > 3 || n < 0 || (n > 0 && (!x || !y)))
     return SCTL_B200_ERR_ARG;
   if (n == 0) return 0;
   int ndev = 0;

@@ -120,7 +120,33 @@ template <class Real> static void run(int G, Long Nt, Long Ns, bool skewed, doub
     g_fail++;
     return;
   }
-  sctl::Vector<Real> U_host(Nt * 3), U_dev(Nt * 3), U_fmm(Nt * 3), U_fmm2(Nt * 3);
+  sctl::Vector<Real> U_host(Nt * 3), U_dev(Nt * 3), U_fmm(Nt * 3), U_fmm2(Nt * 3), U_glue(Nt * 3);
+  // reference for (4): ParticleFMM::EvalDirect with Stokes FxT on densities pre-scaled by the weights (boundary_integral.txx:1036-1051),
+  // then the target-normal dot product on the host (:1060-1071)
+  sctl::Vector<Real> Wq(Ns), Xnt(Nt * 3), Uref_glue(Nt * 3);
+  fill(Wq), fill(Xnt);
+  {
+    using FxT = sctl::GenericKernel<CpuCopy<sctl::kernel_impl::Stokes3D_FxT>>;
+    FxT fxt;
+    sctl::Vector<Real> Fw = Fsl, U9;
+    for (Long i = 0; i < Ns; i++)
+      for (int k = 0; k < 3; k++) Fw[i * 3 + k] *= Wq[i];
+    sctl::ParticleFMM<Real, 3> fmm(sctl::Comm::Self());
+    fmm.SetKernels(fxt, fxt, fxt);
+    fmm.AddTrg("T", fxt, fxt);
+    fmm.AddSrc("S", fxt, fxt);
+    fmm.SetKernelS2T("S", "T", fxt);
+    fmm.SetTrgCoord("T", Xt);
+    fmm.SetSrcCoord("S", Xs);
+    fmm.SetSrcDensity("S", Fw);
+    fmm.EvalDirect(U9, "T");
+    for (Long t = 0; t < Nt; t++)
+      for (int k = 0; k < 3; k++) {
+        Real v = 0;
+        for (int l = 0; l < 3; l++) v += U9[(t * 3 + k) * 3 + l] * Xnt[t * 3 + l];
+        Uref_glue[t * 3 + k] = v;
+      }
+  }
   std::vector<int> fails(G, 0);
   std::vector<std::thread> th;
   for (int rank = 0; rank < G; rank++) {
@@ -190,6 +216,26 @@ template <class Real> static void run(int G, Long Nt, Long Ns, bool skewed, doub
         fmm.Eval(u, "U");
         for (Long i = 0; i < u.Dim(); i++) U_fmm2[t0 * 3 + i] = u[i];
       }
+      {  // (4) the fused ComputeFarField glue in the multi-rank registry: quadrature weights on the sources (gathered like the
+         //     density) and target normals (re-partitioned with the targets when ownership is uneven), Stokes FxT: 9 -> 3 values
+        sctl::Stokes3D_FxT fxt;
+        sctl_b200::ParticleFMM<Real, 3> fmm;
+        fmm.SetComm(comm);
+        fmm.SetKernels(fxt, fxt, fxt);
+        fmm.AddTrg("T", fxt, fxt);
+        fmm.AddSrc("S", fxt, fxt);
+        fmm.SetKernelS2T("S", "T", fxt);
+        fmm.SetTrgCoord("T", xt);
+        fmm.SetSrcCoord("S", xs);
+        fmm.SetSrcDensity("S", fsl);
+        const sctl::Vector<Real> w = slice(Wq, s0, s1, 1), nt = slice(Xnt, t0, t1, 3);
+        fmm.SetSrcWeights("S", w);
+        fmm.SetTrgNormal("T", nt);
+        sctl::Vector<Real> u;
+        fmm.Eval(u, "T");
+        if (u.Dim() != (t1 - t0) * 3) fails[rank]++;
+        for (Long i = 0; i < u.Dim(); i++) U_glue[t0 * 3 + i] = u[i];
+      }
       sctl_b200_comm_destroy(comm);
       // no sctl_b200_finalize here: the thread's streams, events and staging blocks are released when the thread exits
     });
@@ -203,6 +249,7 @@ template <class Real> static void run(int G, Long Nt, Long Ns, bool skewed, doub
   report(tag + " eval_sharded device pointers, FxU then DxU accumulated", rel_l2(U_dev, Uref_both), tol);
   report(tag + " sctl_b200::ParticleFMM + SetComm: DL + SL -> U", rel_l2(U_fmm, Uref_both), tol);
   report(tag + " sctl_b200::ParticleFMM + SetComm after two density updates", rel_l2(U_fmm2, Uref_both), tol);
+  report(tag + " sctl_b200::ParticleFMM + SetComm: Stokes FxT with source weights and target normals", rel_l2(U_glue, Uref_glue), 4 * tol);
   {  // SCTL_B200_ALL_GPUS through the plain host-pointer entry (what -DSCTL_B200_SHIM_FLAGS=SCTL_B200_ALL_GPUS makes the shim pass)
     sctl::Vector<Real> u(Nt * 3);
     u = 0;

@@ -17,7 +17,7 @@ import pytest
 from sctl_b200 import capi
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-MASKED, UNMASKED, UNMASKED_WORST = 1, 0, 2
+MASKED, UNMASKED, UNMASKED_WORST, MASKED_SEL = 1, 0, 2, 3
 DT = {np.dtype(np.float32): capi.F32, np.dtype(np.float64): capi.F64}
 
 
@@ -67,7 +67,7 @@ def test_newton_level_table_cpu():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("dt", [np.float64, np.float32], ids=["f64", "f32"])
-@pytest.mark.parametrize("mode", [MASKED, UNMASKED, UNMASKED_WORST], ids=["masked", "unmasked", "unmasked-worst-seed"])
+@pytest.mark.parametrize("mode", [MASKED, MASKED_SEL, UNMASKED, UNMASKED_WORST], ids=["masked", "masked-branch-free", "unmasked", "unmasked-worst-seed"])
 def test_levels_meet_their_claims_over_the_whole_exponent_range(dt, mode):
     dt = np.dtype(dt)
     x = normal_inputs(dt)
@@ -88,7 +88,7 @@ def test_digits_table_never_delivers_fewer_digits(dt):
     dt = np.dtype(dt)
     x = normal_inputs(dt, per_exp=4, seed=6)
     err = {nw: max_rel(dev_rsqrt(x, nw, UNMASKED_WORST), x) for nw in (0, 1, 2)}
-    err_m = {nw: max_rel(dev_rsqrt(x, nw, MASKED), x) for nw in (0, 1, 2)}
+    err_m = {nw: max(max_rel(dev_rsqrt(x, nw, MASKED), x), max_rel(dev_rsqrt(x, nw, MASKED_SEL), x)) for nw in (0, 1, 2)}
     for digits in list(range(0, 17)) + [-1]:
         lv = capi.lib().sctl_b200_newton_level(DT[dt], digits)
         want_digits = digits if 0 <= digits < 16 else 17
@@ -144,14 +144,15 @@ def test_zero_and_subnormal_arguments(dt):
     sub = sub[(sub > 0) & (sub < fi.tiny)]
     assert sub.size > 32
     for newton in (0, 1, 2):
-        y0 = dev_rsqrt(np.zeros(4, dt), newton, MASKED)
-        assert np.all(y0 == 0) and not np.any(np.signbit(y0))
-        y = dev_rsqrt(sub, newton, MASKED)
-        assert np.all(np.isfinite(y))
-        assert max_rel(y, sub) <= CLAIM[(dt, newton)]
-        # smallest normal numbers: the boundary of the rescaling branch
-        edge = np.array([fi.tiny, fi.tiny * (1 + fi.eps), fi.tiny * 2], dtype=dt)
-        assert max_rel(dev_rsqrt(edge, newton, MASKED), edge) <= CLAIM[(dt, newton)]
+        for masked in (MASKED, MASKED_SEL):
+            y0 = dev_rsqrt(np.zeros(4, dt), newton, masked)
+            assert np.all(y0 == 0) and not np.any(np.signbit(y0))
+            y = dev_rsqrt(sub, newton, masked)
+            assert np.all(np.isfinite(y))
+            assert max_rel(y, sub) <= CLAIM[(dt, newton)]
+            # smallest normal numbers: the boundary of the rescaling branch
+            edge = np.array([fi.tiny, fi.tiny * (1 + fi.eps), fi.tiny * 2], dtype=dt)
+            assert max_rel(dev_rsqrt(edge, newton, masked), edge) <= CLAIM[(dt, newton)]
         for mode in (UNMASKED, UNMASKED_WORST):
             bad = dev_rsqrt(np.concatenate([np.zeros(2, dt), sub]), newton, mode)
             assert not np.any(np.isfinite(bad)), "unmasked rsqrt of a zero/subnormal argument must be non-finite (tile repair trigger)"

@@ -99,6 +99,28 @@ SCTL_B200_API int sctl_b200_eval(int kernel_id, int dtype, int64_t Nt, int64_t N
 SCTL_B200_API int sctl_b200_eval_async(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* d_r_trg, const void* d_r_src,
                          const void* d_n_src, const void* d_v_src, void* d_v_trg, int digits, unsigned flags, void* cuda_stream);
 
+/* sctl_b200_eval_async that allocates NOTHING. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, arithmetic and result as sctl_b200_eval_async; flags may hold SCTL_B200_OVERWRITE only. It always takes the
+ * tiled path (pack -> eval_kernel -> reduce, results bit-identical to sctl_b200_eval_async whenever that picks the same plan) and
+ * keeps the path's working memory - packed source records and per-chunk partial sums - in ONE static __device__ array of
+ * SCTL_B200_NOALLOC_SCRATCH_BYTES (32 MiB) that every GPU loading the library holds until the process exits.
+ * Limit: the packed records, ceil(Ns/256)*256 * record bytes, must fit SCTL_B200_NOALLOC_RECORD_BYTES (24 MiB); a record is
+ * (3 + source payload) Reals rounded up to 16 bytes, at most 80 bytes (Stokes3D_DxU f64), so Ns <= SCTL_B200_NOALLOC_MAX_SRC
+ * (314 368) is accepted for every kernel and dtype, Stokes3D_FxU f64 (48-byte records) up to 524 288. Larger source sets return
+ * SCTL_B200_ERR_ARG with the limit in sctl_b200_last_error() and launch nothing. Nt is not limited: the partial sums use what the
+ * records leave (>= 8 MiB) and the source range is split into fewer chunks when they would not fit.
+ * Calls no cudaMalloc / cudaFree / stream-ordered allocator; the first call on each device resolves the array's address
+ * (cudaGetSymbolAddress, which loads the module: make that call outside a capture).
+ * Every call on a device shares the array: calls are safe when stream order (or events) serialises them; calls that can
+ * OVERLAP on the GPU - different streams, several host threads - race and give undefined results. The array keeps the last
+ * call's contents; no call reads bytes it has not written itself, so nothing needs clearing between calls. */
+#define SCTL_B200_NOALLOC_SCRATCH_BYTES (32u << 20)
+#define SCTL_B200_NOALLOC_RECORD_BYTES (24u << 20)
+#define SCTL_B200_NOALLOC_MAX_SRC 314368
+SCTL_B200_API int sctl_b200_eval_noalloc(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* d_r_trg, const void* d_r_src,
+                           const void* d_n_src, const void* d_v_src, void* d_v_trg, int digits, unsigned flags, void* cuda_stream);
+
 /* Dense operator — replaces GenericKernel::KernelMatrix (generic-kernel.txx:191-307):
  *   M[(s*K0+k0) * (Nt*K1) + (t*K1+k1)] = scale * K[k0][k1](x_t - x_s, n_s)       (row-major, every entry overwritten) */
 SCTL_B200_API int sctl_b200_kernel_matrix(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src,

@@ -17,6 +17,7 @@ LIB_PATH = os.environ.get("SCTL_B200_LIB") or os.path.join(os.path.dirname(os.pa
 F32, F64 = 0, 1
 DEVICE_PTRS, OVERWRITE, ALL_GPUS = 1, 2, 4
 ERR_KERNEL, ERR_DTYPE, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_NCCL = 1, 2, 3, 4, 5, 6
+NOALLOC_SCRATCH_BYTES, NOALLOC_RECORD_BYTES, NOALLOC_MAX_SRC = 32 << 20, 24 << 20, 314368
 
 # every symbol include/sctl_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
@@ -24,6 +25,7 @@ SYMBOLS = {
     "sctl_b200_kernel_name": (c_char_p, [c_int]),
     "sctl_b200_eval": (c_int, [c_int, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_uint]),
     "sctl_b200_eval_async": (c_int, [c_int, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_uint, c_void_p]),
+    "sctl_b200_eval_noalloc": (c_int, [c_int, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_uint, c_void_p]),
     "sctl_b200_kernel_matrix": (c_int, [c_int, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_uint]),
     "sctl_b200_kernel_matrix_async": (c_int, [c_int, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_uint, c_void_p]),
     "sctl_b200_kernel_matrix_batch": (c_int, [c_int, c_int, c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), c_void_p, c_void_p, c_void_p,

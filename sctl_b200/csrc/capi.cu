@@ -302,6 +302,62 @@ int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_
   return eval_packed_device(kernel_id, dtype, Nt, Ns, r_trg, rec.p, v_trg, digits, accumulate, st, sms, ev ? ev + 2 : nullptr);
 }
 
+// The tiled path (pack -> eval_kernel -> reduce) with its working memory placed in a block the CALLER owns instead of two
+// stream-ordered allocations: used by sctl_b200_eval_noalloc (noalloc.cu), which hands in a file-scope __device__ array. No
+// allocation of any kind happens here. Layout of `scratch` (a device address on the current device, 256-byte aligned):
+//   [0, rec_bytes)            packed source records, all Ns_pad of them written by the pack kernel
+//   [round_up(rec_bytes,256)) chunk partial sums [n_chunks][K1][nt_stride] f64, every element that reduce_kernel reads
+//                             (t < Nt) written by eval_kernel's epilogue
+// so nothing in the block has to start at zero and nothing of an earlier call is read. The plan is the one eval_device makes,
+// except that the number of source chunks is cut down to what the rest of the block holds (one chunk needs no partial sums
+// at all: that CTA column then writes v_trg directly). Records larger than rec_max_bytes are refused.
+int eval_device_in_scratch(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                           const void* v_src, void* v_trg, int digits, bool accumulate, cudaStream_t st, int sms, void* scratch,
+                           size_t scratch_bytes, size_t rec_max_bytes) {
+  const EvalEntry& E = (dtype == SCTL_B200_F64 ? eval_table_f64() : eval_table_f32())[kernel_id];
+  const size_t esz = elem_size(dtype);
+  if (Nt == 0) return 0;
+  if (Ns == 0) {
+    if (!accumulate) CU_TRY(cudaMemsetAsync(v_trg, 0, (size_t)Nt * E.k1 * esz, st));
+    return 0;
+  }
+  const size_t rec_one = (size_t)E.rec_len * esz;
+  if ((uint64_t)Ns > rec_max_bytes / rec_one || (size_t)padded_sources(Ns) * rec_one > rec_max_bytes)
+    return set_error(SCTL_B200_ERR_ARG,
+                     "sctl_b200_eval_noalloc: %lld sources of %s need %llu bytes of packed records (%zu bytes each, padded to a multiple of %d "
+                     "sources), the static scratch block holds at most %zu: at most %lld sources for this kernel and dtype - use "
+                     "sctl_b200_eval_async for larger source sets",
+                     (long long)Ns, KINFO[kernel_id].name, (unsigned long long)padded_sources(Ns) * rec_one, rec_one, EVAL_TILE, rec_max_bytes,
+                     (long long)(rec_max_bytes / rec_one / EVAL_TILE * EVAL_TILE));
+  const size_t rec_bytes = (size_t)padded_sources(Ns) * rec_one;
+  const size_t part_off = (rec_bytes + 255) & ~(size_t)255;
+  EvalPlan P = make_plan(E, dtype, Nt, Ns, digits, sms);
+  const size_t per_chunk = (size_t)E.k1 * (size_t)P.nt_stride * sizeof(double);
+  const size_t fit = part_off < scratch_bytes ? (scratch_bytes - part_off) / per_chunk : 0;
+  if (P.n_chunks > 1 && (size_t)P.n_chunks > fit) {
+    const long long chunks = fit >= 2 ? (long long)fit : 1;
+    P.tiles_per_chunk = (int)((P.n_tiles + chunks - 1) / chunks);
+    P.n_chunks = (int)((P.n_tiles + P.tiles_per_chunk - 1) / P.tiles_per_chunk);
+  }
+  char* rec = (char*)scratch;
+  CU_TRY(E.pack(r_src, n_src, v_src, nullptr, rec, Ns, padded_sources(Ns), st));
+  EvalParams p{};
+  p.r_trg = r_trg;
+  p.rec = rec;
+  p.v_trg = v_trg;
+  p.partial = P.n_chunks > 1 ? (double*)((char*)scratch + part_off) : nullptr;
+  p.Nt = Nt;
+  p.nt_stride = P.nt_stride;
+  p.n_tiles = (int)P.n_tiles;
+  p.tiles_per_chunk = P.tiles_per_chunk;
+  p.n_chunks = P.n_chunks;
+  p.accumulate = accumulate ? 1 : 0;
+  p.scale = std::ldexp(kernel_scale(kernel_id), -E.x2_shift[P.newton]);
+  CU_TRY(E.eval[P.rvar][P.newton](p, P.n_ttiles, st));
+  if (P.n_chunks > 1) CU_TRY(E.reduce(p.partial, v_trg, Nt, P.nt_stride, P.n_chunks, p.scale, p.accumulate, st));
+  return 0;
+}
+
 // Sources per CTA of the KernelMatrix kernels (measured, profiles/r02l_kmat_sources_per_cta.txt). Blocks with several values
 // per target (K1out >= 3) write fastest with 8 sources per CTA at every size (Stokes FxU f64: 111 % of the measured copy
 // bandwidth against 106 % at 32; the batched SetupNear shape: 6.2 against 5.5 TB/s); thin rows (one value per target, a 16-byte

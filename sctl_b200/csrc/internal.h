@@ -80,6 +80,12 @@ struct DevBuf {  // grow-only device buffer (cudaMalloc), freed with its owner
 int eval_device(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src, const void* v_src,
                 void* v_trg, int digits, bool accumulate, cudaStream_t st, int sms, cudaEvent_t* ev);
 
+// The same tiled sequence with records and partial sums inside `scratch` (device address, 256-byte aligned, scratch_bytes long)
+// instead of stream-ordered allocations; allocates nothing. Refuses source sets whose packed records exceed rec_max_bytes.
+int eval_device_in_scratch(int kernel_id, int dtype, int64_t Nt, int64_t Ns, const void* r_trg, const void* r_src, const void* n_src,
+                           const void* v_src, void* v_trg, int digits, bool accumulate, cudaStream_t st, int sms, void* scratch,
+                           size_t scratch_bytes, size_t rec_max_bytes);
+
 // ------------------------------------------------------------------------------------------------------------------
 // comm.cu: NCCL communicator handle (sctl_b200_comm_*) and the collectives the registry uses
 // ------------------------------------------------------------------------------------------------------------------

@@ -30,7 +30,7 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 
 KERNEL_ID = 3  # Stokes3D_FxU
-TRAFFIC_4M_BYTES = 1332626432 + 760050432  # ncu, one launch of the 4M x 4M eval_kernel (profiles/r01t_traffic_4m.csv)
+TRAFFIC_4M_BYTES = 1231038976 + 755320576  # ncu, one launch of the 4M x 4M eval_kernel (profiles/r02w_traffic_4m.csv; round 1: 1.33 + 0.76 GB)
 FLOPS_REF = 23  # reference FLOPS() for Stokes3D_FxU (kernel_functions.hpp:79-81): the algorithmic flops per pair
 FP64_INSTR_PER_PAIR = 22  # FP64-pipe instructions our kernel executes per pair (checked in SASS)
 
@@ -413,8 +413,8 @@ def run_b200_arm(args):
     ach = pairs_per_launch * FLOPS_REF / (kern_ms * 1e-3) * 1e-12
     roofline = {"bound": "fp64_cuda_core", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf if peak_tf else None,
                 "traffic": TRAFFIC_4M_BYTES if (args.n == 4_000_000 and world == 1) else None,
-                "traffic_source": "profiles/r01t_traffic_4m.csv: ncu dram__bytes_read.sum + dram__bytes_write.sum of ONE eval_kernel launch at 4M x 4M "
-                                  "(1.33 GB read, 0.76 GB written, over 20.96 s: 0.1 GB/s against 6.5 TB/s; the kernel is FP64-pipe-bound)",
+                "traffic_source": "profiles/r02w_traffic_4m.csv: ncu dram__bytes_read.sum + dram__bytes_write.sum of ONE eval_kernel launch at 4M x 4M "
+                                  "(1.23 GB read, 0.76 GB written, over 20.94 s: 0.1 GB/s against 6.5 TB/s; the kernel is FP64-pipe-bound)",
                 "kernel": "eval_kernel<KStokesFxU,double,R=6,NEWTON=2>", "kernel_ms": kern_ms,
                 "peak_source": "measured live: register-resident DFMA chain (sctl_b200_measure_peak), 2 flop per FMA; MEASURED_PEAKS.json has no FP64 figure",
                 "flops_per_pair_algorithmic": FLOPS_REF, "fp64_instr_per_pair_executed": FP64_INSTR_PER_PAIR,

@@ -40,10 +40,17 @@ namespace sctl_b200 {
 #ifndef SCTL_B200_UNROLL
 #define SCTL_B200_UNROLL 1
 #endif
+#ifndef SCTL_B200_PREFETCH_F32
+#define SCTL_B200_PREFETCH_F32 0  // 1: EVERY FP32 eval_kernel reads the next source record one iteration ahead (sweeps; default: per kernel, PrefetchF32)
+#endif
 constexpr int EVAL_THREADS = SCTL_B200_EVAL_THREADS;  // 4 warps; 2 CTAs/SM at R = 6 (212 registers): ILP, not occupancy, hides the FP64 latency
 constexpr int EVAL_TILE = SCTL_B200_EVAL_TILE;        // sources per shared-memory stage
 constexpr int EVAL_STAGES = SCTL_B200_EVAL_STAGES;    // ring depth (tile k-1's slot is refilled while tile k is consumed)
 constexpr int EVAL_UNROLL = SCTL_B200_UNROLL;         // source-loop unroll factor
+
+// FP32 kernels whose full-precision loop reads the next source record one iteration ahead (see PREFETCH in eval_kernel)
+template <class Ker> struct PrefetchF32 { static constexpr bool value = false; };
+template <> struct PrefetchF32<KLaplaceFxdU> { static constexpr bool value = true; };
 
 struct EvalParams {
   const void* r_trg;  // AoS [Nt*3]
@@ -195,6 +202,12 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
   // one-Newton-step level: Y = 2 rinv with the halving folded into the scale factor (ukernels.cuh "X2 mode"); the caller
   // passes p.scale already divided by 2^X2_SHIFT (eval_x2_shift)
   constexpr bool X2 = eval_x2<Real, NEWTON>();
+  // FP32 only: the source record is read from shared memory one iteration ahead. The f32 loop is short enough per source that
+  // the LDS latency shows at its top (profiles/r02y_stokes_fxu_f32.hotloop.txt), but what the reordering does to the rest of
+  // the schedule depends on the kernel (profiles/r02p_f32_prefetch.txt, all f32 kernels built with -DSCTL_B200_PREFETCH_F32=1:
+  // Laplace FxdU +8.0 %, Laplace FxU +1.1 %, Stokes FxU -1.5 %, Stokes DxU -5.8 %, Stokes FxU at digits 4 -7.3 %), so it is on
+  // only where it was measured to win (PrefetchF32 below). The f64 loop is bound by the FP64 pipe and is left exactly as it is.
+  constexpr bool PREFETCH = (SCTL_B200_PREFETCH_F32 || (PrefetchF32<Ker>::value && NEWTON >= 1)) && sizeof(Real) == 4 && R > 1;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Real* tiles = reinterpret_cast<Real*>(smem_raw);
@@ -256,11 +269,25 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
       for (int q = 0; q < NACC; q++) tacc[r][q] = (Real)0;
     }
 
+    V nxt[PREFETCH ? NV : 1];  // PREFETCH: the record of source s + 1, loaded while source s is being evaluated
+    if constexpr (PREFETCH) {
+#pragma unroll
+      for (int i = 0; i < NV; i++) nxt[i] = tile[i];
+    }
 #pragma unroll EVAL_UNROLL
     for (int s = 0; s < EVAL_TILE; s++) {
       Real src[REC];
+      if constexpr (PREFETCH) {
+        const int sn = s + 1 < EVAL_TILE ? s + 1 : s;
 #pragma unroll
-      for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];  // warp-uniform LDS.128 broadcast
+        for (int i = 0; i < NV; i++) {
+          reinterpret_cast<V*>(src)[i] = nxt[i];
+          nxt[i] = tile[sn * NV + i];
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < NV; i++) reinterpret_cast<V*>(src)[i] = tile[s * NV + i];  // warp-uniform LDS.128 broadcast
+      }
       Real aux[Ker::NAUX > 0 ? Ker::NAUX : 1];
       if (X2) Ker::prep_x2(aux, src + 3);  // once per source, shared by the R targets
 #pragma unroll

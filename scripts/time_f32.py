@@ -5,11 +5,15 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from sctl_b200 import KERNELS, capi, synth
 
-reps = int(sys.argv[1]) if len(sys.argv) > 1 else 5
+reps = int(sys.argv[1]) if len(sys.argv) > 1 else 5  # usage: time_f32.py [REPS] [kid:f32|f64:n:digits,...]
 dev = torch.device("cuda:0")
 print("library:", capi.LIB_PATH)
-for kid, dt, n, digits in ((3, np.float32, 524288, -1), (0, np.float32, 524288, -1), (2, np.float32, 524288, -1), (4, np.float32, 524288, -1),
-                           (3, np.float32, 524288, 4), (3, np.float64, 262144, -1)):
+CASES = ((3, np.float32, 524288, -1), (0, np.float32, 524288, -1), (2, np.float32, 524288, -1), (4, np.float32, 524288, -1),
+         (3, np.float32, 524288, 4), (3, np.float64, 262144, -1))
+if len(sys.argv) > 2:  # kid:f32|f64:n:digits,...
+    DT = {"f32": np.float32, "f64": np.float64}
+    CASES = tuple((int(a), DT[b], int(c), int(d)) for a, b, c, d in (x.split(":") for x in sys.argv[2].split(",")))
+for kid, dt, n, digits in CASES:
     d = capi.kernel_dims(kid)
     Xt, Xs, Xn, F = synth.make_problem(d, n, n, dt)
     t = lambda a: None if a is None else torch.from_numpy(a).to(dev)

@@ -48,9 +48,12 @@ constexpr int EVAL_TILE = SCTL_B200_EVAL_TILE;        // sources per shared-memo
 constexpr int EVAL_STAGES = SCTL_B200_EVAL_STAGES;    // ring depth (tile k-1's slot is refilled while tile k is consumed)
 constexpr int EVAL_UNROLL = SCTL_B200_UNROLL;         // source-loop unroll factor
 
-// FP32 kernels whose full-precision loop reads the next source record one iteration ahead (see PREFETCH in eval_kernel)
-template <class Ker> struct PrefetchF32 { static constexpr bool value = false; };
-template <> struct PrefetchF32<KLaplaceFxdU> { static constexpr bool value = true; };
+// FP32 instantiations that read the next source record one iteration ahead (see PREFETCH in eval_kernel): bit n of `levels` =
+// refinement level NEWTON = n. Only the (kernel, level) pairs that were measured to win (profiles/r02p_f32_prefetch.txt).
+template <class Ker> struct PrefetchF32 { static constexpr int levels = 0; };
+template <> struct PrefetchF32<KLaplaceFxU> { static constexpr int levels = 3; };   // digits 4: +9.0 %, full: +1.0 %
+template <> struct PrefetchF32<KLaplaceFxdU> { static constexpr int levels = 3; };  // digits 4: +2.7 %, full: +8.0 %
+template <> struct PrefetchF32<KStokesFSxU> { static constexpr int levels = 2; };   // full: +3.2 % (digits <= 5 not timed)
 
 struct EvalParams {
   const void* r_trg;  // AoS [Nt*3]
@@ -205,9 +208,10 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
   // FP32 only: the source record is read from shared memory one iteration ahead. The f32 loop is short enough per source that
   // the LDS latency shows at its top (profiles/r02y_stokes_fxu_f32.hotloop.txt), but what the reordering does to the rest of
   // the schedule depends on the kernel (profiles/r02p_f32_prefetch.txt, all f32 kernels built with -DSCTL_B200_PREFETCH_F32=1:
-  // Laplace FxdU +8.0 %, Laplace FxU +1.1 %, Stokes FxU -1.5 %, Stokes DxU -5.8 %, Stokes FxU at digits 4 -7.3 %), so it is on
-  // only where it was measured to win (PrefetchF32 below). The f64 loop is bound by the FP64 pipe and is left exactly as it is.
-  constexpr bool PREFETCH = (SCTL_B200_PREFETCH_F32 || (PrefetchF32<Ker>::value && NEWTON >= 1)) && sizeof(Real) == 4 && R > 1;
+  // Laplace FxdU +8.0 %, Laplace FxU +1.0 % (+9.0 % at digits 4), Stokes FSxU +3.2 %, Laplace DxU -0.5 %, Stokes FxU -1.5 %,
+  // FxUP -3.0 %, DxU -5.8 %, Stokes FxU at digits 4 -7.3 %), so it is on only where it was measured to win (PrefetchF32 above).
+  // The f64 loop is bound by the FP64 pipe and is left exactly as it is.
+  constexpr bool PREFETCH = (SCTL_B200_PREFETCH_F32 || ((PrefetchF32<Ker>::levels >> NEWTON) & 1)) && sizeof(Real) == 4 && R > 1;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Real* tiles = reinterpret_cast<Real*>(smem_raw);

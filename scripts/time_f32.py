@@ -1,5 +1,5 @@
-"""Times the f32 eval kernels of the library SCTL_B200_LIB names (device-resident inputs, CUDA events, best of REPS)."""
-import os, sys
+"""Times eval kernels (default: the f32 ones) of the library SCTL_B200_LIB names (device-resident inputs, CUDA events, best of REPS)."""
+import hashlib, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -29,4 +29,5 @@ for kid, dt, n, digits in CASES:
         e1.record()
         torch.cuda.synchronize()
         best = min(best, e0.elapsed_time(e1))
-    print(f"{d['name']:15s} {np.dtype(dt).name} N={n} digits={digits:2d} best ms={best:.3f} pairs/s={n * n / best * 1e3:.4g}", flush=True)
+    md5 = hashlib.md5(U.cpu().numpy().tobytes()).hexdigest()[:12]  # same bits from two builds = same arithmetic
+    print(f"{d['name']:15s} {np.dtype(dt).name} N={n} digits={digits:2d} best ms={best:.3f} pairs/s={n * n / best * 1e3:.4g} md5(U)={md5}", flush=True)

@@ -40,6 +40,9 @@ namespace sctl_b200 {
 #ifndef SCTL_B200_UNROLL
 #define SCTL_B200_UNROLL 1
 #endif
+#ifndef SCTL_B200_PREFETCH_F64
+#define SCTL_B200_PREFETCH_F64 0  // 1: the same for EVERY FP64 eval_kernel (sweeps)
+#endif
 #ifndef SCTL_B200_PREFETCH_F32
 #define SCTL_B200_PREFETCH_F32 0  // 1: EVERY FP32 eval_kernel reads the next source record one iteration ahead (sweeps; default: per kernel, PrefetchF32)
 #endif
@@ -54,6 +57,7 @@ template <class Ker> struct PrefetchF32 { static constexpr int levels = 0; };
 template <> struct PrefetchF32<KLaplaceFxU> { static constexpr int levels = 3; };   // digits 4: +9.0 %, full: +1.0 %
 template <> struct PrefetchF32<KLaplaceFxdU> { static constexpr int levels = 3; };  // digits 4: +2.7 %, full: +8.0 %
 template <> struct PrefetchF32<KStokesFSxU> { static constexpr int levels = 2; };   // full: +3.2 % (digits <= 5 not timed)
+template <class Ker> struct PrefetchF64 { static constexpr int levels = 0; };  // FP64: none (see PREFETCH)
 
 struct EvalParams {
   const void* r_trg;  // AoS [Nt*3]
@@ -211,7 +215,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) eval_kernel(const EvalPara
   // Laplace FxdU +8.0 %, Laplace FxU +1.0 % (+9.0 % at digits 4), Stokes FSxU +3.2 %, Laplace DxU -0.5 %, Stokes FxU -1.5 %,
   // FxUP -3.0 %, DxU -5.8 %, Stokes FxU at digits 4 -7.3 %), so it is on only where it was measured to win (PrefetchF32 above).
   // The f64 loop is bound by the FP64 pipe and is left exactly as it is.
-  constexpr bool PREFETCH = (SCTL_B200_PREFETCH_F32 || ((PrefetchF32<Ker>::levels >> NEWTON) & 1)) && sizeof(Real) == 4 && R > 1;
+  constexpr bool PREFETCH = R > 1 && (sizeof(Real) == 4 ? (SCTL_B200_PREFETCH_F32 || ((PrefetchF32<Ker>::levels >> NEWTON) & 1))
+                                                        : (SCTL_B200_PREFETCH_F64 || ((PrefetchF64<Ker>::levels >> NEWTON) & 1)));
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Real* tiles = reinterpret_cast<Real*>(smem_raw);

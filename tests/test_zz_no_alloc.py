@@ -180,3 +180,13 @@ def test_argument_checks_need_no_gpu():
     assert L.sctl_b200_eval_noalloc(3, capi.F64, -1, 1, None, None, None, None, None, -1, 0, None) == capi.ERR_ARG
     assert L.sctl_b200_eval_noalloc(3, capi.F64, 1, 1, None, None, None, None, None, -1, 0, None) == capi.ERR_ARG  # null pointers
     assert capi.NOALLOC_MAX_SRC == capi.NOALLOC_RECORD_BYTES // 80 // 256 * 256
+    # the binding's copies of the limits are the header's
+    import os
+    import re
+
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "sctl_b200.h")).read()
+    defs = {k: v for k, v in re.findall(r"#define\s+(SCTL_B200_NOALLOC_\w+)\s+\(?([^)\n]+)\)?", hdr)}
+    val = lambda t: eval(t.replace("u", ""))  # "32u << 20" / "314368"
+    assert val(defs["SCTL_B200_NOALLOC_SCRATCH_BYTES"]) == capi.NOALLOC_SCRATCH_BYTES
+    assert val(defs["SCTL_B200_NOALLOC_RECORD_BYTES"]) == capi.NOALLOC_RECORD_BYTES
+    assert val(defs["SCTL_B200_NOALLOC_MAX_SRC"]) == capi.NOALLOC_MAX_SRC
